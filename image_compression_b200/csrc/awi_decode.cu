@@ -1,0 +1,508 @@
+// awi_decode.cu — AWI payload -> pixels for sm_100a: the inverse of awi_encode.cu.
+//
+// The reference decoder (awi.c:184-217) is serial twice over: a chunk's start is only
+// known once the previous chunk has been parsed (rle.c:134-167: no index, no markers,
+// EOB is not byte aligned inside a chunk) and each DC is a running sum (rle.c:123-128).
+// Here both become scans:
+//
+//   1  dec_scan_segments   every byte offset p of a 2 KB segment speculatively parses the
+//                          chunk that would start there -> L[p]; then each of the 184
+//                          possible entry offsets walks the segment: entry -> (exit, #chunks)
+//   2  dec_compose         32-ary tree of those maps (function composition is associative)
+//   3  dec_expand          top-down: true entry offset + first chunk index of every node
+//   4  dec_emit_offsets    per segment: walk from the true entry, write chunk_off[]
+//   5  dec_dc_*            per-stream (chunk index mod 6) inclusive scan of the DC diffs
+//   6  dec_reconstruct     8 macroblocks per CTA: parse -> dequantise -> IDCT in the
+//                          reference's exact fp64 operation order (dct.c:64-78, zero terms
+//                          skipped) -> 4:2:0 replicate -> inverse colour -> BMP rows / RGB24
+//
+// Steps 1-4 are skipped when the encoder's chunk_off side-info is supplied.
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "codec_math.cuh"
+#include "awi_kernels.h"
+
+namespace awi {
+
+constexpr int SEG = 2048;            // payload bytes per discovery segment
+constexpr int MAXCH = 184;           // longest legal chunk: 12 + 63*(8+15) + 8 bits
+constexpr int SEG_STAGE = SEG + 208; // segment + longest chunk + read-ahead
+constexpr int FAN = 32;              // children per node of the composition tree
+constexpr int DCT_MB = 256;          // macroblocks per DC-scan tile
+constexpr int REC_MB = 8;            // macroblocks per reconstruct CTA
+constexpr int REC_THREADS = REC_MB * 48;
+
+// map entry: bit 63 valid | bits 8..47 chunk count | bits 0..7 exit offset into the next node
+constexpr unsigned long long ENT_OK = 1ull << 63;
+__device__ __forceinline__ unsigned long long ent_make(unsigned long long cnt, int exit) {
+    return ENT_OK | (cnt << 8) | (unsigned long long) exit;
+}
+__device__ __forceinline__ unsigned long long ent_cnt(unsigned long long e) { return (e >> 8) & ((1ull << 40) - 1); }
+__device__ __forceinline__ int ent_exit(unsigned long long e) { return (int) (e & 0xff); }
+
+// ---------------------------------------------------------------- 1: segments
+// Chunk length when parsing from byte s[0] (rle.c:113-167 without producing values);
+// 0 = not a legal chunk (more than 64 coefficients, or longer than MAXCH bytes).
+__device__ __forceinline__ int speculative_len(const uint8_t* s) {
+    int bit = 12, cnt = 1;
+    for (int it = 0; it < 64; it++) {
+        int bi = bit >> 3, sh = 8 - (bit & 7);
+        int sym = ((((int) s[bi] << 8) | (int) s[bi + 1]) >> sh) & 0xff;
+        if (sym == 0) return (bit + 8 + 7) >> 3;
+        cnt += (sym >> 4) + 1;
+        bit += 8 + (sym & 15);
+        if (cnt > 64) return 0;
+    }
+    return 0;
+}
+
+__global__ void __launch_bounds__(256) dec_scan_segments(const uint8_t* __restrict__ payload, unsigned long long P,
+                                                         uint8_t* __restrict__ Lg, unsigned long long* __restrict__ table) {
+    __shared__ __align__(16) uint8_t s[SEG_STAGE];
+    __shared__ uint8_t L[SEG];
+    const unsigned long long seg_start = (unsigned long long) blockIdx.x * SEG;
+    for (int i = threadIdx.x; i < SEG_STAGE; i += 256) {
+        unsigned long long g = seg_start + i;
+        s[i] = g < P ? payload[g] : 0;
+    }
+    __syncthreads();
+    for (int p = threadIdx.x; p < SEG; p += 256) {
+        unsigned long long g = seg_start + p;
+        int len = 0;
+        if (g < P) {
+            len = speculative_len(s + p);
+            if (g + len > P) len = 0;
+        }
+        L[p] = (uint8_t) len;
+        if (g < P) Lg[g] = (uint8_t) len;
+    }
+    __syncthreads();
+    if (threadIdx.x < MAXCH) {
+        int pos = threadIdx.x;
+        unsigned long long cnt = 0;
+        bool ok = true;
+        const long long remain = (long long) (P - seg_start);       // bytes of payload from seg_start on
+        const int lim = remain < SEG ? (int) remain : SEG;
+        if (pos > lim) ok = false;
+        while (ok && pos < lim) {
+            int l = L[pos];
+            if (l == 0) { ok = false; break; }
+            pos += l;
+            cnt++;
+        }
+        // in the last segment a legal chain ends exactly at the payload end
+        if (ok && remain <= SEG && pos != lim) ok = false;
+        int exit = pos - SEG;
+        if (remain <= SEG) exit = 0;
+        table[(unsigned long long) blockIdx.x * MAXCH + threadIdx.x] = ok ? ent_make(cnt, exit) : 0ull;
+    }
+}
+
+// ---------------------------------------------------------------- 2: compose
+__global__ void __launch_bounds__(192) dec_compose(const unsigned long long* __restrict__ in, long long n_in,
+                                                   unsigned long long* __restrict__ out) {
+    if (threadIdx.x >= MAXCH) return;
+    long long c0 = (long long) blockIdx.x * FAN, c1 = c0 + FAN < n_in ? c0 + FAN : n_in;
+    int e = threadIdx.x;
+    unsigned long long cnt = 0;
+    bool ok = true;
+    for (long long c = c0; c < c1; c++) {
+        unsigned long long t = in[c * MAXCH + e];
+        if (!(t & ENT_OK)) { ok = false; break; }
+        cnt += ent_cnt(t);
+        e = ent_exit(t);
+    }
+    out[(long long) blockIdx.x * MAXCH + threadIdx.x] = ok ? ent_make(cnt, e) : 0ull;
+}
+
+// ---------------------------------------------------------------- 3: expand
+// node_in[i] = (entry offset, first chunk index) of parent i; fills the same for its children
+struct NodeState { unsigned long long first_chunk; int entry; int ok; };
+
+__global__ void dec_expand(const unsigned long long* __restrict__ child_table, long long n_child,
+                           const NodeState* __restrict__ parent, long long n_parent, NodeState* __restrict__ child) {
+    long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_parent) return;
+    NodeState st = parent[i];
+    long long c0 = i * FAN, c1 = c0 + FAN < n_child ? c0 + FAN : n_child;
+    for (long long c = c0; c < c1; c++) {
+        child[c] = st;
+        if (st.ok) {
+            unsigned long long t = child_table[c * MAXCH + st.entry];
+            if (t & ENT_OK) { st.first_chunk += ent_cnt(t); st.entry = ent_exit(t); }
+            else st.ok = 0;
+        }
+    }
+}
+
+__global__ void dec_root(const unsigned long long* __restrict__ top_table, NodeState* __restrict__ root,
+                         unsigned long long expect_chunks, unsigned int* err) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    unsigned long long t = top_table[0];
+    NodeState st; st.first_chunk = 0; st.entry = 0; st.ok = 1;
+    if (!(t & ENT_OK) || ent_cnt(t) != expect_chunks) { st.ok = 0; atomicOr(err, 2u); }
+    root[0] = st;
+}
+
+// ---------------------------------------------------------------- 4: offsets
+__global__ void __launch_bounds__(64) dec_emit_offsets(const uint8_t* __restrict__ Lg, unsigned long long P,
+                                                       const NodeState* __restrict__ seg_state,
+                                                       uint32_t* __restrict__ chunk_off, unsigned long long n_chunks) {
+    __shared__ uint8_t L[SEG];
+    const unsigned long long seg_start = (unsigned long long) blockIdx.x * SEG;
+    const long long remain = (long long) (P - seg_start);
+    const int lim = remain < SEG ? (int) remain : SEG;
+    for (int i = threadIdx.x; i < lim; i += 64) L[i] = Lg[seg_start + i];
+    __syncthreads();
+    if (threadIdx.x != 0) return;
+    NodeState st = seg_state[blockIdx.x];
+    if (!st.ok) return;
+    int pos = st.entry;
+    unsigned long long c = st.first_chunk;
+    while (pos < lim && c < n_chunks) {
+        chunk_off[c++] = (uint32_t) (seg_start + pos);
+        int l = L[pos];
+        if (l == 0) break;
+        pos += l;
+    }
+    if (remain <= SEG && c == n_chunks) chunk_off[n_chunks] = (uint32_t) P;
+}
+
+// ---------------------------------------------------------------- 5: DC scan
+// rle.c:118-128: 12-bit field, raw > 2047 means raw - 4095.
+__device__ __forceinline__ int dc_diff_at(const uint8_t* __restrict__ payload, uint32_t off, unsigned long long P) {
+    if ((unsigned long long) off + 2 > P) off = (uint32_t) (P - 2);      // malformed side-info: stay in bounds
+    int raw = ((int) payload[off] << 4) | ((int) payload[off + 1] >> 4);
+    return raw > 2047 ? raw - 4095 : raw;
+}
+
+template <int MODE>   // 0: tile sums   1: apply (inclusive scan + tile base)
+__global__ void __launch_bounds__(DCT_MB) dec_dc_tile(const uint8_t* __restrict__ payload,
+                                                      const uint32_t* __restrict__ chunk_off, long long n_mb,
+                                                      int* __restrict__ tile_sum, const int* __restrict__ tile_base,
+                                                      int* __restrict__ dcabs, unsigned long long P,
+                                                      const unsigned int* __restrict__ err) {
+    __shared__ int wsum[DCT_MB / 32][6];
+    if (*reinterpret_cast<const volatile unsigned int*>(err) != 0) return;     // boundaries unknown: nothing to scan
+    const long long mb = (long long) blockIdx.x * DCT_MB + threadIdx.x;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int v[6];
+#pragma unroll
+    for (int k = 0; k < 6; k++) v[k] = mb < n_mb ? dc_diff_at(payload, chunk_off[mb * 6 + k], P) : 0;
+#pragma unroll
+    for (int k = 0; k < 6; k++) {
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            int t = __shfl_up_sync(0xffffffffu, v[k], o);
+            if (lane >= o) v[k] += t;
+        }
+        if (lane == 31) wsum[warp][k] = v[k];
+    }
+    __syncthreads();
+    if (MODE == 0) {
+        if (threadIdx.x < 6) {
+            int s = 0;
+            for (int w = 0; w < DCT_MB / 32; w++) s += wsum[w][threadIdx.x];
+            tile_sum[(long long) blockIdx.x * 6 + threadIdx.x] = s;
+        }
+    } else {
+        if (mb < n_mb) {
+#pragma unroll
+            for (int k = 0; k < 6; k++) {
+                int base = tile_base[(long long) blockIdx.x * 6 + k];
+                for (int w = 0; w < warp; w++) base += wsum[w][k];
+                dcabs[mb * 6 + k] = base + v[k];
+            }
+        }
+    }
+}
+
+// exclusive scan of the tile sums (one CTA; tiles <= a few thousand)
+__global__ void __launch_bounds__(1024) dec_dc_scan_tiles(const int* __restrict__ tile_sum, long long n_tiles,
+                                                          int* __restrict__ tile_base) {
+    __shared__ int part[1024][6];
+    const long long per = (n_tiles + 1023) / 1024;
+    const long long t0 = (long long) threadIdx.x * per, t1 = t0 + per < n_tiles ? t0 + per : n_tiles;
+    int s[6] = { 0, 0, 0, 0, 0, 0 };
+    for (long long t = t0; t < t1; t++)
+        for (int k = 0; k < 6; k++) s[k] += tile_sum[t * 6 + k];
+    for (int k = 0; k < 6; k++) part[threadIdx.x][k] = s[k];
+    __syncthreads();
+    if (threadIdx.x < 6) {                       // 1024 serial adds per component: negligible
+        int run = 0;
+        for (int i = 0; i < 1024; i++) { int t = part[i][threadIdx.x]; part[i][threadIdx.x] = run; run += t; }
+    }
+    __syncthreads();
+    for (int k = 0; k < 6; k++) s[k] = part[threadIdx.x][k];
+    for (long long t = t0; t < t1; t++)
+        for (int k = 0; k < 6; k++) { tile_base[t * 6 + k] = s[k]; s[k] += tile_sum[t * 6 + k]; }
+}
+
+// ---------------------------------------------------------------- 6: reconstruct
+struct RecSmem {
+    int coef[REC_MB * 6][64];                 // dequantised coefficients, natural [u][v] order
+    unsigned long long mask[REC_MB * 6];      // non-zero positions, natural order
+    double cosd[64];                          // (double) of the reference's fp32 table
+    uint8_t bytes[REC_MB * 6 * MAXCH + 16];   // the tile's slice of the payload
+    uint8_t yp[16][REC_MB * 16];
+    uint8_t cbp[8][REC_MB * 8];
+    uint8_t crp[8][REC_MB * 8];
+    uint8_t scan[64];
+    uint8_t q[2][64];
+};
+
+__device__ __forceinline__ void store_px(const DecParams& P, int x, int y, int r, int g, int b) {
+    if (P.rgb_topdown) {
+        uint8_t* p = P.dst + ((long long) y * P.width + x) * 3;
+        p[0] = (uint8_t) r; p[1] = (uint8_t) g; p[2] = (uint8_t) b;
+    } else {
+        uint8_t* p = P.dst + (long long) (P.height - 1 - y) * P.stride + 3ll * x;
+        p[0] = (uint8_t) b; p[1] = (uint8_t) g; p[2] = (uint8_t) r;
+    }
+}
+
+__global__ void __launch_bounds__(REC_THREADS) dec_reconstruct(DecParams P, const uint32_t* __restrict__ chunk_off,
+                                                               const int* __restrict__ dcabs, unsigned int* err) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    RecSmem& S = *reinterpret_cast<RecSmem*>(smem_raw);
+    const int tid = threadIdx.x;
+    const int tiles_per_row = (P.mbw + REC_MB - 1) / REC_MB;
+    const int my = P.mb_row0 + blockIdx.x / tiles_per_row;
+    const int mx0 = (blockIdx.x % tiles_per_row) * REC_MB;
+    const int n_mb = min(REC_MB, P.mbw - mx0);
+    const long long chunk0 = ((long long) my * P.mbw + mx0) * 6;
+    const int n_ch = n_mb * 6;
+    if (*reinterpret_cast<volatile unsigned int*>(err) != 0) return;          // an earlier stage rejected the stream
+
+    // tables + zeroed coefficients
+    if (tid < 64) {
+        S.cosd[tid] = (double) __uint_as_float(cos_bits_rt(tid));
+        S.scan[tid] = (uint8_t) scan_rt(tid);
+        S.q[0][tid] = (uint8_t) qluma_rt(tid);
+        S.q[1][tid] = (uint8_t) qchroma_rt(tid);
+    }
+    for (int i = tid; i < REC_MB * 6 * 64; i += REC_THREADS) (&S.coef[0][0])[i] = 0;
+    // the tile's chunks are contiguous in the stream
+    const uint32_t b0 = chunk_off[chunk0], b1 = chunk_off[chunk0 + n_ch];
+    if (b1 < b0 || b1 > P.payload_len) { if (tid == 0) atomicOr(err, 4u); return; }
+    const uint32_t nbytes = min(b1 - b0, (uint32_t) (REC_MB * 6 * MAXCH));
+    for (uint32_t i = tid; i < nbytes + 4; i += REC_THREADS) S.bytes[i] = (b0 + i) < P.payload_len ? P.payload[b0 + i] : 0;
+    __syncthreads();
+
+    // ---- parse: one thread per chunk (rle.c:113-170), dequantise (dct.c:128-145) and
+    //      scatter to natural order (dct.c:171-181)
+    if (tid < n_ch) {
+        const int type = tid % 6;
+        const uint8_t* qt = S.q[type >= 4 ? 1 : 0];
+        const uint8_t* s = S.bytes + (chunk_off[chunk0 + tid] - b0);
+        const int limit_bits = (int) (nbytes - (chunk_off[chunk0 + tid] - b0)) * 8;
+        int* out = S.coef[tid];
+        unsigned long long mask = 0;
+        int dc = dcabs[chunk0 + tid] * qt[0];
+        out[0] = dc;
+        if (dc != 0) mask |= 1ull;
+        int bit = 12, idx = 1;
+        bool bad = false;
+        while (true) {
+            if (bit + 8 > limit_bits) { bad = true; break; }
+            int bi = bit >> 3;
+            uint32_t win = ((uint32_t) s[bi] << 24) | ((uint32_t) s[bi + 1] << 16) | ((uint32_t) s[bi + 2] << 8) | s[bi + 3];
+            win <<= (bit & 7);
+            int sym = win >> 24;
+            if (sym == 0) break;
+            int run = sym >> 4, size = sym & 15;
+            idx += run;
+            if (idx > 63) { bad = true; break; }
+            if (size > 0) {
+                int val = (int) ((win << 8) >> (32 - size));
+                int v = (val & (1 << (size - 1))) ? val : val - (1 << size) + 1;      // rle.c:152-155
+                int k = S.scan[idx];
+                int c = v * qt[k];
+                out[k] = c;
+                if (c != 0) mask |= 1ull << k;
+            }
+            idx++;
+            bit += 8 + size;
+        }
+        if (bad) atomicOr(err, 4u);
+        S.mask[tid] = mask;
+    }
+    __syncthreads();
+
+    // ---- IDCT: 8 threads per block, one output row each.  dct.c:64-78: for u, for v:
+    //      sum += (((cu*cv)*coef)*cos[y][u])*cos[x][v], all fp64, strictly in that order.
+    {
+        const int blk = tid >> 3, y = tid & 7;
+        if (blk < n_ch) {
+            double sum[8];
+#pragma unroll
+            for (int x = 0; x < 8; x++) sum[x] = 0.0;
+            unsigned long long m = S.mask[blk];
+            const double inv_sqrt2 = 0.70710678118654746;
+            while (m) {
+                int k = __ffsll((long long) m) - 1;
+                m &= m - 1;
+                int u = k >> 3, v = k & 7;
+                double cu = u == 0 ? inv_sqrt2 : 1.0, cv = v == 0 ? inv_sqrt2 : 1.0;
+                double a = __dmul_rn(__dmul_rn(cu, cv), (double) S.coef[blk][k]);
+                double b = __dmul_rn(a, S.cosd[y * 8 + u]);
+#pragma unroll
+                for (int x = 0; x < 8; x++) sum[x] = __dadd_rn(sum[x], __dmul_rn(b, S.cosd[x * 8 + v]));
+            }
+            const int mb = blk / 6, type = blk - 6 * mb;
+            uint8_t px[8];
+#pragma unroll
+            for (int x = 0; x < 8; x++) px[x] = (uint8_t) clamp_trunc(__dadd_rn(__dmul_rn(0.25, sum[x]), 128.0));
+            uint8_t* dstp;
+            if (type < 4) dstp = &S.yp[((type >> 1) << 3) + y][mb * 16 + ((type & 1) << 3)];
+            else if (type == 4) dstp = &S.cbp[y][mb * 8];
+            else dstp = &S.crp[y][mb * 8];
+            uint2 w;
+            w.x = px[0] | (px[1] << 8) | (px[2] << 16) | ((uint32_t) px[3] << 24);
+            w.y = px[4] | (px[5] << 8) | (px[6] << 16) | ((uint32_t) px[7] << 24);
+            *reinterpret_cast<uint2*>(dstp) = w;
+        }
+    }
+    __syncthreads();
+
+    // ---- 4:2:0 replicate (color.c:88-105) + inverse colour (color.c:45-67) + store with
+    //      cropping (bmp.c:250, :304-308).  4 consecutive pixels per thread.
+    {
+        const int quads_per_row = REC_MB * 4;
+        for (int item = tid; item < 16 * quads_per_row; item += REC_THREADS) {
+            int r = item / quads_per_row, xq = item - r * quads_per_row;
+            int xl = xq * 4;
+            int y = my * 16 + r, x = mx0 * 16 + xl;
+            if (y >= P.height || xl >= n_mb * 16) continue;
+            uint32_t yw = *reinterpret_cast<const uint32_t*>(&S.yp[r][xl]);
+            uint16_t cbw = *reinterpret_cast<const uint16_t*>(&S.cbp[r >> 1][xl >> 1]);
+            uint16_t crw = *reinterpret_cast<const uint16_t*>(&S.crp[r >> 1][xl >> 1]);
+            int R[4], G[4], B[4];
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                int yy = (yw >> (8 * i)) & 0xff;
+                int cb = (cbw >> (8 * (i >> 1))) & 0xff, cr = (crw >> (8 * (i >> 1))) & 0xff;
+                R[i] = red_of(yy, cr); G[i] = green_of(yy, cb, cr); B[i] = blue_of(yy, cb);
+            }
+            uint8_t* p;
+            uint32_t w0, w1, w2;
+            if (P.rgb_topdown) {
+                p = P.dst + ((long long) y * P.width + x) * 3;
+                w0 = R[0] | (G[0] << 8) | (B[0] << 16) | ((uint32_t) R[1] << 24);
+                w1 = G[1] | (B[1] << 8) | (R[2] << 16) | ((uint32_t) G[2] << 24);
+                w2 = B[2] | (R[3] << 8) | (G[3] << 16) | ((uint32_t) B[3] << 24);
+            } else {
+                p = P.dst + (long long) (P.height - 1 - y) * P.stride + 3ll * x;
+                w0 = B[0] | (G[0] << 8) | (R[0] << 16) | ((uint32_t) B[1] << 24);
+                w1 = G[1] | (R[1] << 8) | (B[2] << 16) | ((uint32_t) G[2] << 24);
+                w2 = R[2] | (B[3] << 8) | (G[3] << 16) | ((uint32_t) R[3] << 24);
+            }
+            if (x + 4 <= P.width && (reinterpret_cast<uintptr_t>(p) & 3) == 0) {
+                uint32_t* pw = reinterpret_cast<uint32_t*>(p);
+                pw[0] = w0; pw[1] = w1; pw[2] = w2;
+            } else {
+#pragma unroll
+                for (int i = 0; i < 4; i++)
+                    if (x + i < P.width) store_px(P, x + i, y, R[i], G[i], B[i]);
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------- host side
+static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+struct DecLayout {
+    long long n_seg;
+    int levels;                       // tables[0] = segments ... tables[levels-1] has one node
+    long long n_node[16];
+    size_t off_table[16], off_state[16];
+    size_t off_L, off_chunk_off, off_dcabs, off_tile_sum, off_tile_base, total;
+    long long n_dct;
+};
+
+static DecLayout dec_layout(unsigned long long P, long long n_chunks) {
+    DecLayout Lo{};
+    Lo.n_seg = (long long) ((P + SEG - 1) / SEG);
+    if (Lo.n_seg < 1) Lo.n_seg = 1;
+    size_t off = 0;
+    long long n = Lo.n_seg;
+    int lv = 0;
+    while (true) {
+        Lo.n_node[lv] = n;
+        Lo.off_table[lv] = off; off = align_up(off + (size_t) n * MAXCH * 8, 256);
+        Lo.off_state[lv] = off; off = align_up(off + (size_t) n * sizeof(NodeState), 256);
+        lv++;
+        if (n == 1) break;
+        n = (n + FAN - 1) / FAN;
+    }
+    Lo.levels = lv;
+    Lo.off_L = off; off = align_up(off + (size_t) P + 16, 256);
+    Lo.off_chunk_off = off; off = align_up(off + (size_t) (n_chunks + 1) * 4, 256);
+    Lo.off_dcabs = off; off = align_up(off + (size_t) n_chunks * 4, 256);
+    Lo.n_dct = (n_chunks / 6 + DCT_MB - 1) / DCT_MB;
+    Lo.off_tile_sum = off; off = align_up(off + (size_t) Lo.n_dct * 6 * 4, 256);
+    Lo.off_tile_base = off; off = align_up(off + (size_t) Lo.n_dct * 6 * 4, 256);
+    Lo.total = off;
+    return Lo;
+}
+
+size_t dec_workspace_bytes(unsigned long long payload_len, long long n_chunks) {
+    return dec_layout(payload_len, n_chunks).total;
+}
+
+cudaError_t launch_decode(const DecParams& P, void* workspace, size_t workspace_bytes,
+                          const uint32_t* chunk_off_in, unsigned int* err, cudaStream_t stream) {
+    const long long n_mb = (long long) P.mbw * P.mbh;
+    const long long n_chunks = n_mb * 6;
+    DecLayout Lo = dec_layout(P.payload_len, n_chunks);
+    if (workspace_bytes < Lo.total) return cudaErrorInvalidValue;
+    uint8_t* ws = static_cast<uint8_t*>(workspace);
+    uint32_t* chunk_off = reinterpret_cast<uint32_t*>(ws + Lo.off_chunk_off);
+
+    if (chunk_off_in == nullptr) {
+        uint8_t* Lg = ws + Lo.off_L;
+        auto table = [&](int lv) { return reinterpret_cast<unsigned long long*>(ws + Lo.off_table[lv]); };
+        auto state = [&](int lv) { return reinterpret_cast<NodeState*>(ws + Lo.off_state[lv]); };
+        dec_scan_segments<<<(unsigned) Lo.n_seg, 256, 0, stream>>>(P.payload, P.payload_len, Lg, table(0));
+        for (int lv = 1; lv < Lo.levels; lv++)
+            dec_compose<<<(unsigned) Lo.n_node[lv], 192, 0, stream>>>(table(lv - 1), Lo.n_node[lv - 1], table(lv));
+        dec_root<<<1, 32, 0, stream>>>(table(Lo.levels - 1), state(Lo.levels - 1), (unsigned long long) n_chunks, err);
+        for (int lv = Lo.levels - 1; lv >= 1; lv--) {
+            long long np = Lo.n_node[lv];
+            dec_expand<<<(unsigned) ((np + 127) / 128), 128, 0, stream>>>(table(lv - 1), Lo.n_node[lv - 1], state(lv), np,
+                                                                       state(lv - 1));
+        }
+        dec_emit_offsets<<<(unsigned) Lo.n_seg, 64, 0, stream>>>(Lg, P.payload_len, state(0), chunk_off,
+                                                                (unsigned long long) n_chunks);
+    } else {
+        cudaError_t e = cudaMemcpyAsync(chunk_off, chunk_off_in, (size_t) n_chunks * 4, cudaMemcpyDeviceToDevice, stream);
+        if (e != cudaSuccess) return e;
+        uint32_t end = (uint32_t) P.payload_len;
+        e = cudaMemcpyAsync(chunk_off + n_chunks, &end, 4, cudaMemcpyHostToDevice, stream);
+        if (e != cudaSuccess) return e;
+    }
+
+    int* dcabs = reinterpret_cast<int*>(ws + Lo.off_dcabs);
+    int* tile_sum = reinterpret_cast<int*>(ws + Lo.off_tile_sum);
+    int* tile_base = reinterpret_cast<int*>(ws + Lo.off_tile_base);
+    dec_dc_tile<0><<<(unsigned) Lo.n_dct, DCT_MB, 0, stream>>>(P.payload, chunk_off, n_mb, tile_sum, nullptr, nullptr, P.payload_len, err);
+    dec_dc_scan_tiles<<<1, 1024, 0, stream>>>(tile_sum, Lo.n_dct, tile_base);
+    dec_dc_tile<1><<<(unsigned) Lo.n_dct, DCT_MB, 0, stream>>>(P.payload, chunk_off, n_mb, nullptr, tile_base, dcabs, P.payload_len, err);
+
+    static bool attr_set[64] = { false };
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 64 && !attr_set[dev]) {
+        cudaError_t e = cudaFuncSetAttribute(dec_reconstruct, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sizeof(RecSmem));
+        if (e != cudaSuccess) return e;
+        attr_set[dev] = true;
+    }
+    const int tiles_per_row = (P.mbw + REC_MB - 1) / REC_MB;
+    const int rows = P.mb_row1 - P.mb_row0;
+    if (rows > 0)
+        dec_reconstruct<<<(unsigned) (tiles_per_row * rows), REC_THREADS, sizeof(RecSmem), stream>>>(P, chunk_off, dcabs, err);
+    return cudaGetLastError();
+}
+
+}  // namespace awi

@@ -1,0 +1,400 @@
+// awi_encode.cu — fused BMP-rows -> AWI payload encoder for sm_100a.
+//
+// One kernel replaces the body of the reference's macroblock loop
+// (awi.c:94-128: read_block -> rgb_block16_to_ycbcr -> ycbcr_block_subsample ->
+// 6 x [dct_block -> quantize_block -> zigzag_block -> rle_encode_chunk_and_write])
+// and the bit-serial writer underneath it (bitrw.c:9-43):
+//
+//   tile = 32 consecutive macroblocks (raster order), one CTA of 6 warps
+//   A  coalesced 128-bit loads of the tile's 16 pixel rows (bottom-up BGR) -> smem
+//   B  one thread per 8x8 block: colour -> AAN DCT -> quantise (+ambiguity flags)
+//      -> scan-order int8 coefficients in smem;  exact DC;  halo macroblock DCs
+//   C  flagged coefficients recomputed warp-cooperatively in the reference's exact
+//      operation order
+//   D  one thread per chunk: run-length symbols + bit packing into a smem slot
+//   E  CTA scan of chunk byte lengths + decoupled look-back across tiles
+//   F  byte scatter of the slots to their final payload offsets
+//
+// Chunks are byte aligned (rle.c:107) so the device-wide scan is over BYTE lengths.
+// The only cross-tile state, the six DC predictors (awi.c:91-92), is rebuilt from a
+// one-macroblock halo with the integer DC formula, so tiles (and stripes on other
+// GPUs) never wait on each other for data — only for the output offset.
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "codec_math.cuh"
+#include "awi_kernels.h"
+
+namespace awi {
+
+constexpr int TILE_MB = ENC_TILE_MB;             // 32 macroblocks per tile
+constexpr int THREADS = 192;                     // one thread per 8x8 block of the tile
+constexpr int NWARPS = THREADS / 32;
+constexpr int ROW_BYTES = TILE_MB * 48;          // one pixel row of the tile in smem
+constexpr int RAW_BYTES = 16 * ROW_BYTES;        // 24576
+constexpr int SLOT = 124;                        // staging bytes per chunk (max 121), 31 words: conflict-free
+static_assert(THREADS * SLOT <= RAW_BYTES, "chunk slots alias the raw tile");
+
+struct __align__(16) EncSmem {
+    uint8_t raw[RAW_BYTES];                      // phase A-C: pixels; phase D-F: chunk slots
+    uint8_t halo[16 * 48];                       // macroblock preceding the tile
+    uint32_t coef[THREADS * 16];                 // int8[64] per block, scan order, quads swizzled
+    unsigned long long amb[THREADS];             // per block: natural positions to recompute
+    float cosf[64];
+    int dc[(TILE_MB + 1) * 6];                   // quantised DCs, [0] = halo macroblock
+    int halo_sum[6];
+    uint32_t len[THREADS];                       // chunk byte lengths, chunk order
+    uint32_t off[THREADS];                       // exclusive offsets inside the tile
+    uint32_t warp_tot[NWARPS];
+    unsigned long long tile_base;
+    int tile;
+};
+
+// thread -> block mapping.  Warps 0..3: luma, block row i = warp&1, macroblock half
+// hm = warp>>1, lane = 2*m' + j (so a warp reads 32 horizontally adjacent 8-pixel
+// groups: 24-byte lane stride, conflict-free 64-bit smem loads).  Warps 4,5: chroma,
+// hm = warp-4, lanes 0-15 Cb, 16-31 Cr of macroblock m' = lane&15.
+struct BlockId { int mb; int type; };            // type: 0..3 = Y[i][j], 4 = Cb, 5 = Cr
+__device__ __forceinline__ BlockId block_of(int tid) {
+    int w = tid >> 5, l = tid & 31;
+    BlockId b;
+    if (w < 4) { b.mb = ((w >> 1) << 4) + (l >> 1); b.type = ((w & 1) << 1) | (l & 1); }
+    else { b.mb = ((w - 4) << 4) + (l & 15); b.type = 4 + (l >> 4); }
+    return b;
+}
+__device__ __forceinline__ int thread_of(int mb, int type) {
+    if (type < 4) return ((((mb >> 4) << 1) | (type >> 1)) << 5) + ((mb & 15) << 1) + (type & 1);
+    return ((4 + (mb >> 4)) << 5) + ((type - 4) << 4) + (mb & 15);
+}
+__device__ __forceinline__ int coef_word(int tid, int word) {      // swizzled word index
+    return tid * 16 + ((((word >> 2) ^ (tid >> 1)) & 3) << 2) + (word & 3);
+}
+
+__device__ __forceinline__ uint64_t ld_desc(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_desc(unsigned long long* p, unsigned long long v) {
+    asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+// ---------------------------------------------------------------- phase A
+// bmp.c:48-119 addressing.  Pixel bytes outside the image read as zero (bmp.c:89-93,106-109).
+__device__ __forceinline__ uint4 load_piece(const EncParams& P, int mb_global, int row, int k) {
+    int my = mb_global / P.mbw, mx = mb_global - my * P.mbw;
+    int y = my * 16 + row;
+    int xb = mx * 48 + k * 16;
+    uint4 v = make_uint4(0, 0, 0, 0);
+    int valid = P.width * 3 - xb;                      // bytes of this piece inside the image row
+    if (y >= P.height || valid <= 0) return v;
+    const uint8_t* src = P.rows + (long long) (P.height - 1 - y) * P.stride + xb;
+    if (valid >= 16) {
+        if (P.align == 16) return __ldg(reinterpret_cast<const uint4*>(src));
+        if (P.align == 4) {
+            const uint32_t* s = reinterpret_cast<const uint32_t*>(src);
+            return make_uint4(__ldg(s), __ldg(s + 1), __ldg(s + 2), __ldg(s + 3));
+        }
+        valid = 16;
+    }
+    uint32_t w[4] = { 0, 0, 0, 0 };
+    for (int i = 0; i < valid; i++) w[i >> 2] |= (uint32_t) __ldg(src + i) << (8 * (i & 3));
+    return make_uint4(w[0], w[1], w[2], w[3]);
+}
+
+// ---------------------------------------------------------------- phase B helpers
+__device__ __forceinline__ int byte_of(uint32_t w, int i) { return (int) ((w >> (8 * i)) & 0xffu); }
+
+// 8 pixels (24 bytes B,G,R,...) in 6 words -> 8 centred luma samples
+__device__ __forceinline__ void luma_row(const uint32_t* w, float* d) {
+#pragma unroll
+    for (int x = 0; x < 8; x++) {
+        int b = byte_of(w[(3 * x) >> 2], (3 * x) & 3);
+        int g = byte_of(w[(3 * x + 1) >> 2], (3 * x + 1) & 3);
+        int r = byte_of(w[(3 * x + 2) >> 2], (3 * x + 2) & 3);
+        d[x] = centred(luma_of(r, g, b));
+    }
+}
+
+// one colour-difference sample; cr selects the coefficient set (warp-divergent only in
+// the value of three registers, not in control flow, except for the rare exact path)
+__device__ __forceinline__ int chroma_of(int r, int g, int b, bool cr) {
+    int kr = cr ? 5000 : -1687, kg = cr ? -4187 : -3313, kb = cr ? -813 : 5000;
+    uint32_t n = (uint32_t) (kr * r + kg * g + kb * b + 1280000);
+    uint32_t q = __umulhi(n, 3435974u) >> 3;
+    if (n - q * 10000u == 0u) return cr ? cr_exact(r, g, b) : cb_exact(r, g, b);
+    return (int) q;
+}
+
+// 16 pixels (48 bytes) in 12 words -> samples of the 8 even pixels (color.c:82-83)
+__device__ __forceinline__ void chroma_row(const uint32_t* w, float* d, bool cr) {
+#pragma unroll
+    for (int x = 0; x < 8; x++) {
+        int b = byte_of(w[(6 * x) >> 2], (6 * x) & 3);
+        int g = byte_of(w[(6 * x + 1) >> 2], (6 * x + 1) & 3);
+        int r = byte_of(w[(6 * x + 2) >> 2], (6 * x + 2) & 3);
+        d[x] = centred(chroma_of(r, g, b, cr));
+    }
+}
+
+// sample (row y, column x) of the block owned by thread `tid`, recomputed from raw pixels
+__device__ __forceinline__ int sample_of(const EncSmem& S, int tid, int y, int x) {
+    BlockId id = block_of(tid);
+    int row, col;
+    if (id.type < 4) { row = ((id.type >> 1) << 3) + y; col = id.mb * 48 + ((id.type & 1) * 8 + x) * 3; }
+    else { row = 2 * y; col = id.mb * 48 + 6 * x; }
+    const uint8_t* p = S.raw + row * ROW_BYTES + col;
+    int b = p[0], g = p[1], r = p[2];
+    if (id.type < 4) return luma_of(r, g, b);
+    return chroma_of(r, g, b, id.type == 5);
+}
+
+// ---------------------------------------------------------------- the kernel
+__global__ void __launch_bounds__(THREADS, 3) awi_encode_kernel(EncParams P) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    EncSmem& S = *reinterpret_cast<EncSmem*>(smem_raw);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+    // ticketed tile order: a tile only ever waits on tiles whose CTAs already run
+    if (tid == 0) S.tile = (int) atomicAdd(P.ticket, 1u);
+    if (tid < 64) S.cosf[tid] = __uint_as_float(cos_bits_rt(tid));
+    if (tid < 6) S.halo_sum[tid] = 0;
+    __syncthreads();
+    const int tile = S.tile;
+    const int mb_first = P.mb0 + tile * TILE_MB;                 // global raster index
+    const int n_mb = min(TILE_MB, P.mb1 - mb_first);
+    const bool has_halo = mb_first > 0;
+
+    // ---- A: stage pixels
+    {
+        uint4* dst = reinterpret_cast<uint4*>(S.raw);
+        constexpr int PIECES = 16 * TILE_MB * 3;
+#pragma unroll 8
+        for (int p = tid; p < PIECES; p += THREADS) {
+            int row = p / (3 * TILE_MB), rem = p - row * (3 * TILE_MB);
+            int m = rem / 3, k = rem - 3 * m;
+            uint4 v = make_uint4(0, 0, 0, 0);
+            if (m < n_mb) v = load_piece(P, mb_first + m, row, k);
+            dst[p] = v;
+        }
+        if (tid < 48) {
+            uint4 v = make_uint4(0, 0, 0, 0);
+            if (has_halo) v = load_piece(P, mb_first - 1, tid / 3, tid % 3);
+            reinterpret_cast<uint4*>(S.halo)[tid] = v;
+        }
+    }
+    __syncthreads();
+
+    // ---- B: colour + DCT + quantise, one block per thread
+    const BlockId me = block_of(tid);
+    const bool active = me.mb < n_mb;
+    uint64_t amb = 0;
+    if (active) {
+        float d[64];
+        uint32_t packed[16];
+        if (warp < 4) {
+            const uint8_t* base = S.raw + ((me.type >> 1) << 3) * ROW_BYTES + me.mb * 48 + (me.type & 1) * 24;
+#pragma unroll
+            for (int y = 0; y < 8; y++) {
+                const uint2* src = reinterpret_cast<const uint2*>(base + y * ROW_BYTES);
+                uint2 a = src[0], b = src[1], c = src[2];
+                uint32_t w[6] = { a.x, a.y, b.x, b.y, c.x, c.y };
+                luma_row(w, d + 8 * y);
+            }
+            fdct_quant_pack<false>(d, packed, amb);
+        } else {
+            const uint8_t* base = S.raw + me.mb * 48;
+            const bool cr = me.type == 5;
+#pragma unroll
+            for (int y = 0; y < 8; y++) {
+                const uint4* src = reinterpret_cast<const uint4*>(base + 2 * y * ROW_BYTES);
+                uint4 a = src[0], b = src[1], c = src[2];
+                uint32_t w[12] = { a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w, c.x, c.y, c.z, c.w };
+                chroma_row(w, d + 8 * y, cr);
+            }
+            fdct_quant_pack<true>(d, packed, amb);
+        }
+#pragma unroll
+        for (int q4 = 0; q4 < 4; q4++) {
+            uint4 v = make_uint4(packed[4 * q4], packed[4 * q4 + 1], packed[4 * q4 + 2], packed[4 * q4 + 3]);
+            *reinterpret_cast<uint4*>(&S.coef[coef_word(tid, 4 * q4)]) = v;
+        }
+        S.dc[(me.mb + 1) * 6 + me.type] = (int) (int8_t) (packed[0] & 0xff);
+    }
+    S.amb[tid] = amb;
+
+    // halo macroblock: only the six block sums are needed (integer DC formula)
+    if (has_halo) {
+        if (tid < 128) {
+            int p = 2 * tid, py = p >> 4, px = p & 15;
+            const uint8_t* q = S.halo + py * 48 + px * 3;
+            int s = luma_of(q[2], q[1], q[0]) + luma_of(q[5], q[4], q[3]);
+            s += __shfl_xor_sync(0xffffffffu, s, 1);
+            s += __shfl_xor_sync(0xffffffffu, s, 2);
+            s += __shfl_xor_sync(0xffffffffu, s, 8);
+            s += __shfl_xor_sync(0xffffffffu, s, 16);
+            if ((lane & 27) == 0) atomicAdd(&S.halo_sum[((py >> 3) << 1) | (px >> 3)], s);
+        } else {
+            int t = tid - 128, yy = t >> 3, xx = t & 7;
+            const uint8_t* q = S.halo + 2 * yy * 48 + 6 * xx;
+            int cb = chroma_of(q[2], q[1], q[0], false), cr = chroma_of(q[2], q[1], q[0], true);
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                cb += __shfl_xor_sync(0xffffffffu, cb, o);
+                cr += __shfl_xor_sync(0xffffffffu, cr, o);
+            }
+            if (lane == 0) { atomicAdd(&S.halo_sum[4], cb); atomicAdd(&S.halo_sum[5], cr); }
+        }
+    }
+    const int any_amb = __syncthreads_or(amb != 0);
+
+    if (tid < 6)
+        S.dc[tid] = has_halo ? quant_int(dc_coef_from_sum(S.halo_sum[tid] - 128 * 64), tid < 4 ? 16 : 17) : 0;
+
+    // ---- C: exact recomputation of flagged coefficients (dct.c:26-53 operation order)
+    if (any_amb) {
+        for (int b = warp; b < THREADS; b += NWARPS) {
+            unsigned long long m = S.amb[b];
+            const bool chroma = b >= 128;
+            while (m) {
+                int k = __ffsll((long long) m) - 1;
+                m &= m - 1;
+                int u = k >> 3, v = k & 7;
+                int y = lane >> 2, x0 = (lane & 3) * 2;
+                float cyu = S.cosf[y * 8 + u];
+                double part = (double) exact_product(sample_of(S, b, y, x0) - 128, cyu, S.cosf[x0 * 8 + v]);
+                part += (double) exact_product(sample_of(S, b, y, x0 + 1) - 128, cyu, S.cosf[(x0 + 1) * 8 + v]);
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+                if (lane == 0) {
+                    int c = exact_coef_finish(part, u, v);
+                    int q = quant_int(c, chroma ? qchroma_rt(k) : qluma_rt(k));
+                    int idx = unscan_rt(k);
+                    reinterpret_cast<int8_t*>(&S.coef[coef_word(b, idx >> 2)])[idx & 3] = (int8_t) q;
+                }
+            }
+        }
+    }
+    __syncthreads();                                   // raw pixels are dead from here on
+
+    // ---- D: run-length + bit packing, one chunk per thread, into its slot
+    uint32_t my_len = 0;
+    if (active) {
+        uint32_t w[16];
+#pragma unroll
+        for (int q4 = 0; q4 < 4; q4++) {
+            uint4 v = *reinterpret_cast<const uint4*>(&S.coef[coef_word(tid, 4 * q4)]);
+            w[4 * q4] = v.x; w[4 * q4 + 1] = v.y; w[4 * q4 + 2] = v.z; w[4 * q4 + 3] = v.w;
+        }
+        uint32_t lo = 0, hi = 0;
+#pragma unroll
+        for (int i = 0; i < 16; i++) {
+            // 0x80 in every non-zero byte, then gather the four flags into a nibble
+            uint32_t nz = (((w[i] & 0x7f7f7f7fu) + 0x7f7f7f7fu) | w[i]) & 0x80808080u;
+            uint32_t nib = ((nz >> 7) * 0x10204080u) >> 28;
+            if (i < 8) lo |= nib << (4 * i); else hi |= nib << (4 * (i - 8));
+        }
+        const uint8_t* cbase = reinterpret_cast<const uint8_t*>(S.coef);
+        const int swz = (tid >> 1) & 3;
+        auto coef = [&](int i) -> int {
+            return (int) (int8_t) cbase[tid * 64 + ((((i >> 4) ^ swz) & 3) << 4) + (i & 15)];
+        };
+        uint32_t* slot = reinterpret_cast<uint32_t*>(S.raw + tid * SLOT);
+        auto put = [&](int word, uint32_t be) { slot[word] = __byte_perm(be, 0, 0x0123); };
+        int dc = S.dc[(me.mb + 1) * 6 + me.type];
+        int prev = S.dc[me.mb * 6 + me.type];
+        my_len = (uint32_t) rle_chunk(dc, prev, ((unsigned long long) hi << 32) | lo, coef, put);
+    }
+    S.len[me.mb * 6 + me.type] = my_len;
+    __syncthreads();
+
+    // ---- E: offsets inside the tile (chunk order = tid order here), then across tiles
+    {
+        uint32_t v = S.len[tid], incl = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += t;
+        }
+        if (lane == 31) S.warp_tot[warp] = incl;
+        __syncthreads();
+        uint32_t wbase = 0, total = 0;
+#pragma unroll
+        for (int i = 0; i < NWARPS; i++) { uint32_t t = S.warp_tot[i]; if (i < warp) wbase += t; total += t; }
+        S.off[tid] = wbase + incl - v;
+
+        if (warp == 0) {
+            constexpr unsigned long long FLAG_AGG = 1ull << 62, FLAG_PFX = 2ull << 62, VMASK = (1ull << 62) - 1;
+            unsigned long long excl = 0;
+            if (tile > 0) {
+                if (lane == 0) st_desc(P.desc + tile, FLAG_AGG | total);
+                int base = tile - 1;
+                while (true) {
+                    int idx = base - lane;
+                    unsigned long long dsc = FLAG_PFX;                // virtual prefix 0 before tile 0
+                    if (idx >= 0) { do { dsc = ld_desc(P.desc + idx); } while ((dsc >> 62) == 0); }
+                    unsigned pm = __ballot_sync(0xffffffffu, (dsc >> 62) == 2);
+                    int first = pm ? (__ffs((int) pm) - 1) : 31;
+                    unsigned long long c = lane <= first ? (dsc & VMASK) : 0ull;
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+                    excl += c;
+                    if (pm) break;
+                    base -= 32;
+                }
+            }
+            if (lane == 0) {
+                st_desc(P.desc + tile, FLAG_PFX | (excl + total));
+                S.tile_base = excl;
+                if (mb_first + n_mb >= P.mb1) *P.out_len = excl + total;      // last tile: payload length
+            }
+        }
+    }
+    __syncthreads();
+
+    // ---- F: scatter the chunk bytes
+    {
+        const unsigned long long base = S.tile_base;
+        const int c = tid;                               // chunk index inside the tile
+        const int mb = c / 6, type = c - 6 * mb;
+        const uint32_t L = S.len[c], O = S.off[c];
+        const int owner = thread_of(mb, type);
+        const long long gchunk = (long long) (mb_first - P.mb0) * 6 + c;
+        const bool fits = base + S.off[THREADS - 1] + S.len[THREADS - 1] <= P.out_cap;
+        if (!fits && tid == 0) atomicOr(P.err, 1u);
+        if (P.chunk_off != nullptr && mb < n_mb) P.chunk_off[gchunk] = (uint32_t) (base + O);
+        if (P.qcoef != nullptr && mb < n_mb) {
+            uint32_t* dst = reinterpret_cast<uint32_t*>(P.qcoef + gchunk * 64);
+#pragma unroll
+            for (int i = 0; i < 16; i++) dst[i] = S.coef[coef_word(owner, i)];
+        }
+        if (fits) {
+            for (int j = 0; j < 32; j++) {
+                uint32_t Lj = __shfl_sync(0xffffffffu, L, j);
+                uint32_t Oj = __shfl_sync(0xffffffffu, O, j);
+                int ownj = __shfl_sync(0xffffffffu, owner, j);
+                const uint8_t* src = S.raw + ownj * SLOT;
+                uint8_t* dst = P.out + base + Oj;
+                for (uint32_t i = lane; i < Lj; i += 32) dst[i] = src[i];
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------- launch
+size_t enc_smem_bytes() { return sizeof(EncSmem); }
+
+cudaError_t launch_encode(const EncParams& P, int n_tiles, cudaStream_t stream) {
+    static bool attr_set[64] = { false };
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 64 && !attr_set[dev]) {
+        cudaError_t e = cudaFuncSetAttribute(awi_encode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int) sizeof(EncSmem));
+        if (e != cudaSuccess) return e;
+        attr_set[dev] = true;
+    }
+    awi_encode_kernel<<<n_tiles, THREADS, sizeof(EncSmem), stream>>>(P);
+    return cudaGetLastError();
+}
+
+}  // namespace awi

@@ -1,0 +1,71 @@
+// awi_kernels.h — internal interface between the C-ABI layer (gpu_codec.cu) and the
+// kernel translation units.  Not installed; the public surface is include/gpu_codec.h.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+#include "codec_tables.h"
+
+namespace awi {
+
+constexpr int ENC_TILE_MB = 32;      // macroblocks per encode tile (one CTA)
+
+// Run-time indexed copies of the generated tables (device global memory; the hot loops
+// use the constexpr accessors in codec_math.cuh, which fold into immediates).
+static __device__ const int d_qluma[64] = AWI_QLUMA;
+static __device__ const int d_qchroma[64] = AWI_QCHROMA;
+static __device__ const int d_unscan[64] = AWI_UNSCAN;
+static __device__ const int d_scan[64] = AWI_SCAN;
+static __device__ const uint32_t d_cos_bits[64] = AWI_COS_BITS;
+__device__ __forceinline__ int qluma_rt(int k) { return d_qluma[k]; }
+__device__ __forceinline__ int qchroma_rt(int k) { return d_qchroma[k]; }
+__device__ __forceinline__ int unscan_rt(int k) { return d_unscan[k]; }
+__device__ __forceinline__ int scan_rt(int i) { return d_scan[i]; }
+__device__ __forceinline__ uint32_t cos_bits_rt(int i) { return d_cos_bits[i]; }
+
+// ---- encode
+struct EncParams {
+    const uint8_t* rows;          // address of bottom-up row 0 of the FULL image (may lie outside the
+                                  // caller's window; only rows the tile range needs are dereferenced)
+    long long stride;             // bytes between rows
+    int width, height;            // full image
+    int align;                    // 16, 4 or 1: guaranteed alignment of rows and stride
+    int mbw;                      // macroblocks per row
+    int mb0, mb1;                 // raster macroblock range [mb0, mb1) to encode
+    uint8_t* out;                 // payload bytes for this range
+    unsigned long long out_cap;
+    unsigned long long* out_len;  // payload length, written by the last tile
+    unsigned long long* desc;     // one look-back descriptor per tile, zeroed before launch
+    unsigned int* ticket;         // zeroed before launch
+    unsigned int* err;            // bit 0: out_cap too small
+    uint32_t* chunk_off;          // optional: byte offset of every chunk in `out`
+    int8_t* qcoef;                // optional: quantised coefficients, 64 per chunk, scan order
+};
+size_t enc_smem_bytes();
+cudaError_t launch_encode(const EncParams& P, int n_tiles, cudaStream_t stream);
+
+// ---- decode
+struct DecParams {
+    const uint8_t* payload;
+    unsigned long long payload_len;
+    int width, height, mbw, mbh;
+    int mb_row0, mb_row1;          // macroblock rows to reconstruct (parse covers everything before)
+    uint8_t* dst;                  // address of output row 0 (bottom-up BGR) or of pixel (0,0) (RGB24)
+    long long stride;              // bytes between output rows (BGR) — RGB24 uses 3*width
+    int rgb_topdown;               // 0: bottom-up BGR rows (bmp.c:222-260); 1: packed top-down RGB24 (bmp.c:291-320)
+};
+struct DecWorkspace {
+    // sized by dec_workspace_bytes(); all device memory
+    uint8_t* base;
+    size_t bytes;
+};
+size_t dec_workspace_bytes(unsigned long long payload_len, long long n_chunks);
+// chunk_off_in: optional encoder side-info (skips boundary discovery when non-null)
+cudaError_t launch_decode(const DecParams& P, void* workspace, size_t workspace_bytes,
+                          const uint32_t* chunk_off_in, unsigned int* err, cudaStream_t stream);
+
+// ---- misc kernels (gpu_codec.cu)
+cudaError_t launch_synth(uint8_t* rows, int width, int height, long long stride, int kind, uint32_t seed,
+                         int frame, cudaStream_t stream);
+
+}  // namespace awi

@@ -1,0 +1,352 @@
+// codec_math.cuh — per-pixel / per-block arithmetic of the AWI hot path, written once
+// and used by the sm_100a kernels (awi_encode.cu, awi_decode.cu).  tests/emul/ compiles
+// the same header for the host (AWI_HD empty) so the exactness argument can be checked
+// against the oracle without a GPU; that build is a test harness, not a product path.
+//
+// Exactness contract (reference file:line in each function).  Everything here must
+// give the reference's result bit for bit.  Where the reference's own operation order
+// is too slow to run for every sample (dct.c:26-53 is 4096 two-rounding fp32 products
+// plus 4096 fp64 adds per block) a FAST path computes an approximation with a proven
+// error bound and flags every result that could differ; flagged results are recomputed
+// with the reference's exact operation sequence.  Unflagged results are provably equal.
+#pragma once
+#include <stdint.h>
+#include "codec_tables.h"
+
+#if defined(__CUDACC__)
+#define AWI_HD __host__ __device__ __forceinline__
+#define AWI_D __device__ __forceinline__
+#else
+#include <math.h>
+#include <string.h>
+#define AWI_HD inline
+#endif
+
+namespace awi {
+
+// ------------------------------------------------------------------ bit helpers
+AWI_HD uint32_t f2u(float f) {
+#if defined(__CUDA_ARCH__)
+    return __float_as_uint(f);
+#else
+    uint32_t u; memcpy(&u, &f, 4); return u;
+#endif
+}
+AWI_HD float u2f(uint32_t u) {
+#if defined(__CUDA_ARCH__)
+    return __uint_as_float(u);
+#else
+    float f; memcpy(&f, &u, 4); return f;
+#endif
+}
+AWI_HD float fma_rn(float a, float b, float c) {
+#if defined(__CUDA_ARCH__)
+    return __fmaf_rn(a, b, c);
+#else
+    return fmaf(a, b, c);
+#endif
+}
+// IEEE single operations that must never be contracted into an FMA
+AWI_HD float mul_rn(float a, float b) {
+#if defined(__CUDA_ARCH__)
+    return __fmul_rn(a, b);
+#else
+    volatile float r = a * b; return r;
+#endif
+}
+AWI_HD double dmul_rn(double a, double b) {
+#if defined(__CUDA_ARCH__)
+    return __dmul_rn(a, b);
+#else
+    volatile double r = a * b; return r;
+#endif
+}
+AWI_HD double dadd_rn(double a, double b) {
+#if defined(__CUDA_ARCH__)
+    return __dadd_rn(a, b);
+#else
+    volatile double r = a + b; return r;
+#endif
+}
+AWI_HD uint32_t umulhi32(uint32_t a, uint32_t b) {
+#if defined(__CUDA_ARCH__)
+    return __umulhi(a, b);
+#else
+    return (uint32_t) (((uint64_t) a * b) >> 32);
+#endif
+}
+AWI_HD uint32_t byte_perm(uint32_t a, uint32_t b, uint32_t s) {
+#if defined(__CUDA_ARCH__)
+    return __byte_perm(a, b, s);
+#else
+    uint64_t t = ((uint64_t) b << 32) | a; uint32_t r = 0;
+    for (int i = 0; i < 4; i++) r |= (uint32_t) ((t >> (8 * ((s >> (4 * i)) & 7))) & 0xff) << (8 * i);
+    return r;
+#endif
+}
+
+// ------------------------------------------------------------------ constant tables
+// constexpr accessors: after full unrolling every index is a literal, so the values
+// fold into instruction immediates.
+#define AWI_TABLE_FN(name, type, init) \
+    AWI_HD constexpr type name(int k) { constexpr type t[64] = init; return t[k]; }
+AWI_TABLE_FN(qluma, int, AWI_QLUMA)
+AWI_TABLE_FN(qchroma, int, AWI_QCHROMA)
+AWI_TABLE_FN(scan_tab, int, AWI_SCAN)
+AWI_TABLE_FN(unscan_tab, int, AWI_UNSCAN)
+AWI_TABLE_FN(gk_luma, float, AWI_GK_LUMA)
+AWI_TABLE_FN(gc_luma, float, AWI_GC_LUMA)
+AWI_TABLE_FN(gt_luma, float, AWI_GT_LUMA)
+AWI_TABLE_FN(gk_chroma, float, AWI_GK_CHROMA)
+AWI_TABLE_FN(gc_chroma, float, AWI_GC_CHROMA)
+AWI_TABLE_FN(gt_chroma, float, AWI_GT_CHROMA)
+AWI_TABLE_FN(cos_bits, uint32_t, AWI_COS_BITS)
+
+// ------------------------------------------------------------------ forward colour
+// color.c:31-33 + utils.c:10-17.  The reference evaluates decimal-coefficient sums in
+// fp64 and truncates.  The sums are integers over 1000 (Y) or 10000 (Cb, Cr), so the
+// integer quotient equals the truncated fp64 value unless the numerator is an exact
+// multiple (then fp64 may land one ulp below the integer: 3464 / 0 / 688 of the 2^24
+// inputs).  Exact multiples take the literal fp64 expression.
+AWI_HD int clamp_trunc(double v) { return v > 255 ? 255 : (v < 0 ? 0 : (int) v); }
+
+AWI_HD int y_exact(int r, int g, int b) {
+    return clamp_trunc(dadd_rn(dadd_rn(dmul_rn(0.299, (double) r), dmul_rn(0.587, (double) g)), dmul_rn(0.114, (double) b)));
+}
+AWI_HD int cb_exact(int r, int g, int b) {
+    // -0.1687*r - 0.3313*g + 0.5*b + 128, left to right
+    double t = dadd_rn(dmul_rn(-0.1687, (double) r), -dmul_rn(0.3313, (double) g));
+    t = dadd_rn(t, dmul_rn(0.5, (double) b));
+    return clamp_trunc(dadd_rn(t, 128.0));
+}
+AWI_HD int cr_exact(int r, int g, int b) {
+    double t = dadd_rn(dmul_rn(0.5, (double) r), -dmul_rn(0.4187, (double) g));
+    t = dadd_rn(t, -dmul_rn(0.0813, (double) b));
+    return clamp_trunc(dadd_rn(t, 128.0));
+}
+
+AWI_HD int luma_of(int r, int g, int b) {
+    uint32_t n = (uint32_t) (299 * r + 587 * g + 114 * b);            // <= 255000
+    uint32_t q = umulhi32(n, 4294968u);                              // n / 1000 (verified for n <= 255000)
+    if (n - q * 1000u == 0u) return y_exact(r, g, b);
+    return (int) q;
+}
+// chroma numerators are >= 5000 so plain floor division is truncation
+AWI_HD int cb_of(int r, int g, int b) {
+    uint32_t n = (uint32_t) (-1687 * r - 3313 * g + 5000 * b + 1280000);
+    uint32_t q = umulhi32(n, 3435974u) >> 3;                         // n / 10000 (verified for n <= 2560000)
+    if (n - q * 10000u == 0u) return cb_exact(r, g, b);
+    return (int) q;
+}
+AWI_HD int cr_of(int r, int g, int b) {
+    uint32_t n = (uint32_t) (5000 * r - 4187 * g - 813 * b + 1280000);
+    uint32_t q = umulhi32(n, 3435974u) >> 3;
+    if (n - q * 10000u == 0u) return cr_exact(r, g, b);
+    return (int) q;
+}
+
+// ------------------------------------------------------------------ inverse colour
+// color.c:61-63 + utils.c:10-17: fp64, left to right, (cb-128)/(cr-128) are int before
+// promotion, truncating clamp.  Same trick as forward: the values are integers over
+// 1000 (R, B) or 10^6 (G); only exact multiples can land on the other side of an
+// integer in fp64 (0 / 34 / 0 of the 2^24 inputs), those take the literal expression.
+AWI_HD int r_exact(int y, int cr) { return clamp_trunc(dadd_rn((double) y, dmul_rn(1.402, (double) (cr - 128)))); }
+AWI_HD int g_exact(int y, int cb, int cr) {
+    double t = dadd_rn((double) y, -dmul_rn(0.344136, (double) (cb - 128)));
+    return clamp_trunc(dadd_rn(t, -dmul_rn(0.714136, (double) (cr - 128))));
+}
+AWI_HD int b_exact(int y, int cb) { return clamp_trunc(dadd_rn((double) y, dmul_rn(1.772, (double) (cb - 128)))); }
+
+AWI_HD int clamp_div(int n, int d, uint32_t magic, int shift, bool& exact_multiple) {
+    // n / d truncated and clamped to 0..255; d in {1000, 125000}
+    exact_multiple = false;
+    if (n <= 0) { exact_multiple = (n == 0); return 0; }
+    if (n >= 255 * d) { exact_multiple = (n == 255 * d); return 255; }
+    uint32_t q = umulhi32((uint32_t) n, magic) >> shift;
+    exact_multiple = ((uint32_t) n - q * (uint32_t) d) == 0u;
+    return (int) q;
+}
+AWI_HD int red_of(int y, int cr) {
+    bool ex; int v = clamp_div(1000 * y + 1402 * (cr - 128), 1000, 4294968u, 0, ex);
+    return ex ? r_exact(y, cr) : v;
+}
+AWI_HD int green_of(int y, int cb, int cr) {
+    // every term of 10^6*y - 344136*(cb-128) - 714136*(cr-128) is a multiple of 8: work in
+    // eighths (divisor 125000); 2^44/125000 -> magic 140737489 is exact for n <= 255*125000.
+    bool ex; int v = clamp_div(125000 * y - 43017 * (cb - 128) - 89267 * (cr - 128), 125000, 140737489u, 12, ex);
+    return ex ? g_exact(y, cb, cr) : v;
+}
+AWI_HD int blue_of(int y, int cb) {
+    bool ex; int v = clamp_div(1000 * y + 1772 * (cb - 128), 1000, 4294968u, 0, ex);
+    return ex ? b_exact(y, cb) : v;
+}
+
+// sample (0..255) -> (float)(sample - 128) without an int->float conversion:
+// 0x4B000000 | s is the float 2^23 + s.
+AWI_HD float centred(int s) { return u2f(0x4B000000u | (uint32_t) s) - 8388736.0f; }
+
+// ------------------------------------------------------------------ forward DCT, fast path
+// 8-point AAN butterfly (5 multiplies, 29 adds), outputs scaled by a_k (a_0 = 1,
+// a_k = sqrt2*cos(k*pi/16)) relative to the orthonormal-free sum  sum_x d[x] cos((2x+1)k pi/16).
+// With integer inputs |d| <= 2^21 output 0 (the plain sum) and 4 are exact.
+AWI_HD void aan8(float& d0, float& d1, float& d2, float& d3, float& d4, float& d5, float& d6, float& d7) {
+    float t0 = d0 + d7, t7 = d0 - d7, t1 = d1 + d6, t6 = d1 - d6;
+    float t2 = d2 + d5, t5 = d2 - d5, t3 = d3 + d4, t4 = d3 - d4;
+    float t10 = t0 + t3, t13 = t0 - t3, t11 = t1 + t2, t12 = t1 - t2;
+    d0 = t10 + t11;
+    d4 = t10 - t11;
+    float z1 = (t12 + t13) * 0.707106781f;
+    d2 = t13 + z1;
+    d6 = t13 - z1;
+    t10 = t4 + t5; t11 = t5 + t6; t12 = t6 + t7;
+    float z5 = (t10 - t12) * 0.382683433f;
+    float z2 = fma_rn(0.541196100f, t10, z5);
+    float z4 = fma_rn(1.306562965f, t12, z5);
+    float z3 = t11 * 0.707106781f;
+    float z11 = t7 + z3, z13 = t7 - z3;
+    d5 = z13 + z2; d3 = z13 - z2;
+    d1 = z11 + z4; d7 = z11 - z4;
+}
+
+// Quantised DC from the exact sample sum S = sum(p - 128)  (dct.c:50 at u=v=0: the fp64
+// scale 0.25*cu*cv is 0x3FBFFFFFFFFFFFFE, a hair under 1/8, so (int)(scale*S) is
+// sign(S)*((|S|-1)>>3); then dct.c:123 round-half-away = (2|c|+Q)/(2Q)).
+AWI_HD int dc_coef_from_sum(int S) {
+    int a = S < 0 ? -S : S;
+    int c = a == 0 ? 0 : ((a - 1) >> 3);
+    return S < 0 ? -c : c;
+}
+AWI_HD int quant_int(int c, int Q) {
+    int a = c < 0 ? -c : c;
+    int q = (2 * a + Q) / (2 * Q);
+    return c < 0 ? -q : q;
+}
+
+// Fast DCT + quantise + scan-order pack of one 8x8 block held in registers.
+//   d[64]  in: centred samples, natural [y][x] order (destroyed)
+//   packed out: 64 int8 quantised coefficients in chunk (scan) order, 4 per word, LE
+//   amb    out: bit k set <=> natural position k must be recomputed exactly
+// Position 0 (DC) is exact and never flagged.
+template <bool CHROMA>
+AWI_HD void fdct_quant_pack(float* d, uint32_t* packed, uint64_t& amb) {
+#pragma unroll
+    for (int y = 0; y < 8; y++)
+        aan8(d[8 * y + 0], d[8 * y + 1], d[8 * y + 2], d[8 * y + 3], d[8 * y + 4], d[8 * y + 5], d[8 * y + 6], d[8 * y + 7]);
+#pragma unroll
+    for (int x = 0; x < 8; x++)
+        aan8(d[x], d[8 + x], d[16 + x], d[24 + x], d[32 + x], d[40 + x], d[48 + x], d[56 + x]);
+
+    uint32_t lo = 0, hi = 0;
+    const float MAGIC = 12582912.0f;   // 1.5 * 2^23: low mantissa bits of (g + MAGIC) are rn(g) in two's complement
+#pragma unroll
+    for (int k = 1; k < 64; k++) {
+        const float gk = CHROMA ? gk_chroma(k) : gk_luma(k);
+        const float gc = CHROMA ? gc_chroma(k) : gc_luma(k);
+        const float gt = CHROMA ? gt_chroma(k) : gt_luma(k);
+        float x = d[k];
+        float g;
+        if (gc != 0.0f) {
+            float sc = u2f(f2u(gc) | ((f2u(x) & 0x80000000u) ^ 0x80000000u));   // -sign(x)*gc
+            g = fma_rn(x, gk, sc);
+        } else {
+            g = x * gk;
+        }
+        float t = g + MAGIC;
+        float n = t - MAGIC;
+        float diff = g - n;
+        bool a = (diff < 0 ? -diff : diff) > gt;
+        if (k < 32) lo |= a ? (1u << k) : 0u; else hi |= a ? (1u << (k - 32)) : 0u;
+        d[k] = t;
+    }
+    // exact DC: d[0] is the integer sum of the 64 centred samples
+    {
+        int S = (int) d[0];
+        int q = quant_int(dc_coef_from_sum(S), CHROMA ? 17 : 16);
+        d[0] = u2f((uint32_t) q);       // only the low byte is used below
+    }
+    amb = ((uint64_t) hi << 32) | lo;
+#pragma unroll
+    for (int w = 0; w < 16; w++) {
+        uint32_t a = byte_perm(f2u(d[scan_tab(4 * w)]), f2u(d[scan_tab(4 * w + 1)]), 0x0040);
+        uint32_t b = byte_perm(f2u(d[scan_tab(4 * w + 2)]), f2u(d[scan_tab(4 * w + 3)]), 0x0040);
+        packed[w] = byte_perm(a, b, 0x5410);
+    }
+}
+
+// ------------------------------------------------------------------ forward DCT, exact path
+// dct.c:26-53 for ONE output (u,v): sum over y,x of fl32(fl32(b*cos[y][u])*cos[x][v]) is
+// exact in fp64 (|terms| are multiples of 2^-28 below 2^7, 64 of them), so any order
+// gives the reference's sum; then ((0.25*cu)*cv)*sum in fp64, truncate, quantise.
+AWI_HD double fdct_scale(int u, int v) {
+    const double inv_sqrt2 = 0.70710678118654746;     // 1.0/sqrt(2.0) = 0x3FE6A09E667F3BCC
+    double cu = u == 0 ? inv_sqrt2 : 1.0, cv = v == 0 ? inv_sqrt2 : 1.0;
+    return dmul_rn(dmul_rn(0.25, cu), cv);
+}
+AWI_HD float exact_product(int centred_sample, float cyu, float cxv) {
+    return mul_rn(mul_rn((float) centred_sample, cyu), cxv);
+}
+AWI_HD int exact_coef_finish(double sum, int u, int v) {
+    return (int) dmul_rn(fdct_scale(u, v), sum);
+}
+
+// ------------------------------------------------------------------ RLE of one chunk
+// rle.c:52-110 + bitrw.c:9-43.  `coef(i)` returns chunk[i] (scan order, int8 range);
+// `put32(word_index, big_endian_word)` stores 4 output bytes.  Returns the chunk's byte
+// length (3..121).  The caller provides the non-zero mask of positions 1..63.
+struct BitAcc {
+    uint64_t acc = 0;   // bits not yet flushed sit in the low `cnt` bits
+    int cnt = 0;
+    int words = 0;
+};
+
+template <class Put>
+AWI_HD void bits_push(BitAcc& s, uint32_t value, int width, Put& put32) {
+    s.acc = (s.acc << width) | value;
+    s.cnt += width;
+    if (s.cnt >= 32) {
+        put32(s.words++, (uint32_t) (s.acc >> (s.cnt - 32)));
+        s.cnt -= 32;
+    }
+}
+
+AWI_HD int bit_length_u(uint32_t a) {
+#if defined(__CUDA_ARCH__)
+    return 32 - __clz((int) a);
+#else
+    int n = 0; while (a) { n++; a >>= 1; } return n;
+#endif
+}
+AWI_HD int lowest_set64(uint64_t m) {
+#if defined(__CUDA_ARCH__)
+    return __ffsll((long long) m) - 1;
+#else
+    return __builtin_ctzll(m);
+#endif
+}
+
+template <class Coef, class Put>
+AWI_HD int rle_chunk(int dc, int prev_dc, uint64_t nzmask, Coef coef, Put put32) {
+    BitAcc s;
+    int diff = dc - prev_dc;
+    bits_push(s, (uint32_t) (diff >= 0 ? diff : 4095 + diff) & 0xFFFu, 12, put32);      // rle.c:53-57
+    int prev = 0;
+    uint64_t m = nzmask & ~1ull;
+    while (m) {
+        int i = lowest_set64(m);
+        m &= m - 1;
+        int gap = i - prev - 1;
+        prev = i;
+        for (int z = gap >> 4; z > 0; z--) bits_push(s, 0xF0u, 8, put32);               // rle.c:70-83
+        int v = coef(i);
+        uint32_t a = (uint32_t) (v < 0 ? -v : v);
+        int size = bit_length_u(a);
+        uint32_t field = v > 0 ? (uint32_t) v : (uint32_t) ((1 << size) - 1 + v);       // rle.c:86-92
+        bits_push(s, ((uint32_t) ((gap & 15) << 4 | size) << size) | field, 8 + size, put32);
+    }
+    bits_push(s, 0u, 8, put32);                                                          // EOB, rle.c:106
+    int nbytes = 4 * s.words + ((s.cnt + 7) >> 3);                                        // rle.c:107 pad
+    if (s.cnt > 0) put32(s.words, (uint32_t) (s.acc << (32 - s.cnt)));
+    return nbytes;
+}
+
+}  // namespace awi

@@ -1,0 +1,507 @@
+// gpu_codec.cu — the C ABI declared in include/gpu_codec.h: contexts, scratch and staging
+// management, stripe / batch partitioning over GPUs and host-side stitching.  No codec
+// arithmetic lives here (see awi_encode.cu / awi_decode.cu) and there is no CPU path:
+// without a usable CUDA device every entry point reports failure.
+#include <cuda_runtime.h>
+#include <stdarg.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <mutex>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "../../include/gpu_codec.h"
+#include "awi_kernels.h"
+#include "codec_math.cuh"
+
+namespace {
+
+thread_local std::string g_last_error;
+
+bool fail(const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    g_last_error = buf;
+    fprintf(stderr, "gpu_codec: %s\n", buf);      // reference convention: one stderr line, return false
+    return false;
+}
+
+#define CU(call)                                                                                  \
+    do {                                                                                          \
+        cudaError_t e__ = (call);                                                                 \
+        if (e__ != cudaSuccess) return fail("%s failed: %s", #call, cudaGetErrorString(e__));     \
+    } while (0)
+
+constexpr size_t ENC_WS_HEADER = 256;     // [0,8) payload length, [8,12) tile ticket
+
+struct Buf {
+    uint8_t* p = nullptr;
+    size_t bytes = 0;
+};
+
+struct Ctx {
+    int dev = -1;
+    cudaStream_t stream = nullptr;
+    Buf enc_ws, dec_ws, in, out;
+    unsigned int* d_err = nullptr;
+    uint64_t* h_len = nullptr;                // pinned
+    std::mutex mu;
+};
+
+std::vector<Ctx*> g_ctx;
+std::mutex g_mu;
+
+bool ensure(Buf& b, size_t bytes) {
+    if (b.bytes >= bytes) return true;
+    if (b.p) CU(cudaFree(b.p));
+    b.p = nullptr;
+    b.bytes = 0;
+    size_t want = bytes + bytes / 8 + 4096;
+    CU(cudaMalloc(&b.p, want));
+    b.bytes = want;
+    return true;
+}
+
+Ctx* get_ctx(int i) {
+    if (i < 0 || i >= (int) g_ctx.size()) {
+        fail("context %d not initialised (call gpu_codec_init first)", i);
+        return nullptr;
+    }
+    return g_ctx[i];
+}
+
+void destroy_ctx(Ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->dev);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    for (Buf* b : { &c->enc_ws, &c->dec_ws, &c->in, &c->out })
+        if (b->p) cudaFree(b->p);
+    if (c->d_err) cudaFree(c->d_err);
+    if (c->h_len) cudaFreeHost(c->h_len);
+    delete c;
+}
+
+inline int align_of(const void* p, long long stride) {
+    uintptr_t a = reinterpret_cast<uintptr_t>(p);
+    if (a % 16 == 0 && stride % 16 == 0) return 16;
+    if (a % 4 == 0 && stride % 4 == 0) return 4;
+    return 1;
+}
+
+// -------------------------------------------------------------- small kernels
+
+__global__ void synth_kernel(uint8_t* rows, int width, int height, long long stride, int kind, uint32_t seed, int frame) {
+    // image_compression_b200/synth.py restated; one thread per byte of the pixel array
+    long long n = (long long) width * height * 3;
+    for (long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long) gridDim.x * blockDim.x) {
+        long long pix = i / 3;
+        int c = (int) (i - pix * 3);             // 0,1,2 = R,G,B
+        int y = (int) (pix / width), x = (int) (pix - (long long) y * width);
+        int v;
+        if (kind == 2) {
+            v = 144;
+        } else {
+            uint32_t s = seed ^ ((uint32_t) frame * 0x9E3779B9u);
+            uint32_t h = (uint32_t) i * 0x9E3779B1u + s;
+            h ^= h >> 16; h *= 0x85EBCA6Bu; h ^= h >> 13; h *= 0xC2B2AE35u; h ^= h >> 16;
+            if (kind == 0) {
+                v = (int) (h >> 24);
+            } else {
+                int t1 = 3 * x + 37 * c + 5 * frame, t2 = 2 * y + 91 * c;
+                int tri1 = abs((t1 & 511) - 256) - 128, tri2 = abs((t2 & 511) - 256) - 128;
+                v = 128 + ((tri1 + tri2) >> 1) + ((int) (h >> 27) - 16);
+                v = v < 0 ? 0 : (v > 255 ? 255 : v);
+            }
+        }
+        rows[(long long) (height - 1 - y) * stride + 3ll * x + (2 - c)] = (uint8_t) v;
+    }
+}
+
+__global__ void pad_zero_kernel(uint8_t* rows, int width, int height, long long stride) {
+    int pad = (int) (stride - 3ll * width);
+    long long n = (long long) pad * height;
+    for (long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long) gridDim.x * blockDim.x)
+        rows[(i / pad) * stride + 3ll * width + (i % pad)] = 0;
+}
+
+__global__ void colour_kernel(const uint8_t* in, size_t n, int inverse, uint8_t* out) {
+    for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t) gridDim.x * blockDim.x) {
+        int a = in[3 * i], b = in[3 * i + 1], c = in[3 * i + 2];
+        if (!inverse) {
+            out[3 * i] = (uint8_t) awi::luma_of(a, b, c);
+            out[3 * i + 1] = (uint8_t) awi::cb_of(a, b, c);
+            out[3 * i + 2] = (uint8_t) awi::cr_of(a, b, c);
+        } else {
+            out[3 * i] = (uint8_t) awi::red_of(a, c);
+            out[3 * i + 1] = (uint8_t) awi::green_of(a, b, c);
+            out[3 * i + 2] = (uint8_t) awi::blue_of(a, b);
+        }
+    }
+}
+
+// -------------------------------------------------------------- device-resident bodies
+
+bool encode_dev_impl(Ctx* c, const uint8_t* d_rows, int width, int height, long long stride, int wy0, int wy1,
+                     int r0, int r1, uint8_t* d_payload, size_t cap, uint64_t* d_len, uint32_t* d_chunk_off,
+                     int8_t* d_qcoef, cudaStream_t st) {
+    if (width <= 0 || height <= 0) return fail("encode: bad geometry %dx%d", width, height);
+    if (stride < 3ll * width) return fail("encode: row_stride %lld < 3*width", stride);
+    const int mbw = (width + 15) / 16, mbh = (height + 15) / 16;
+    if (r0 < 0 || r1 > mbh || r0 >= r1) return fail("encode: bad macroblock row range [%d,%d) of %d", r0, r1, mbh);
+    if ((long long) mbw * mbh > (1ll << 30)) return fail("encode: frame too large");
+    const int need_lo = r0 > 0 ? 16 * r0 - 16 : 0, need_hi = 16 * r1 < height ? 16 * r1 : height;
+    if (wy0 > need_lo || wy1 < need_hi || wy1 > height || wy0 < 0)
+        return fail("encode: pixel window [%d,%d) does not cover rows [%d,%d)", wy0, wy1, need_lo, need_hi);
+    if (!d_rows || !d_payload) return fail("encode: null device pointer");
+
+    const long long n_mb = (long long) (r1 - r0) * mbw;
+    const int n_tiles = (int) ((n_mb + awi::ENC_TILE_MB - 1) / awi::ENC_TILE_MB);
+    CU(cudaSetDevice(c->dev));
+    const size_t ws_bytes = ENC_WS_HEADER + (size_t) n_tiles * 8;
+    if (!ensure(c->enc_ws, ws_bytes)) return false;
+    CU(cudaMemsetAsync(c->enc_ws.p, 0, ws_bytes, st));
+
+    awi::EncParams P{};
+    // address of bottom-up row 0 of the full frame, had the whole frame been resident
+    P.rows = d_rows - (long long) (height - wy1) * stride;
+    P.stride = stride;
+    P.width = width;
+    P.height = height;
+    P.align = align_of(d_rows, stride);
+    P.mbw = mbw;
+    P.mb0 = r0 * mbw;
+    P.mb1 = r1 * mbw;
+    P.out = d_payload;
+    P.out_cap = cap;
+    P.out_len = reinterpret_cast<unsigned long long*>(c->enc_ws.p);
+    P.ticket = reinterpret_cast<unsigned int*>(c->enc_ws.p + 8);
+    P.desc = reinterpret_cast<unsigned long long*>(c->enc_ws.p + ENC_WS_HEADER);
+    P.err = c->d_err;
+    P.chunk_off = d_chunk_off;
+    P.qcoef = d_qcoef;
+    CU(awi::launch_encode(P, n_tiles, st));
+    if (d_len) CU(cudaMemcpyAsync(d_len, c->enc_ws.p, 8, cudaMemcpyDeviceToDevice, st));
+    return true;
+}
+
+bool decode_dev_impl(Ctx* c, const uint8_t* d_payload, size_t len, int width, int height, int r0, int r1,
+                     uint8_t* d_dst, long long stride, int rgb, const uint32_t* d_chunk_off, cudaStream_t st) {
+    if (width <= 0 || height <= 0) return fail("decode: bad geometry %dx%d", width, height);
+    const int mbw = (width + 15) / 16, mbh = (height + 15) / 16;
+    if (r0 < 0 || r1 > mbh || r0 > r1) return fail("decode: bad macroblock row range [%d,%d) of %d", r0, r1, mbh);
+    if (!rgb && stride < 3ll * width) return fail("decode: row_stride %lld < 3*width", stride);
+    if (len >= (1ull << 32) - 256) return fail("decode: payload of %zu bytes is too large", len);
+    const long long n_chunks = (long long) mbw * mbh * 6;
+    if (len < (size_t) n_chunks * 3) return fail("decode: payload of %zu bytes is shorter than %lld chunks", len, n_chunks);
+    if (!d_payload || !d_dst) return fail("decode: null device pointer");
+    CU(cudaSetDevice(c->dev));
+    const size_t ws = awi::dec_workspace_bytes(len, n_chunks);
+    if (!ensure(c->dec_ws, ws)) return false;
+    awi::DecParams P{};
+    P.payload = d_payload;
+    P.payload_len = len;
+    P.width = width;
+    P.height = height;
+    P.mbw = mbw;
+    P.mbh = mbh;
+    P.mb_row0 = r0;
+    P.mb_row1 = r1;
+    P.dst = d_dst;
+    P.stride = stride;
+    P.rgb_topdown = rgb ? 1 : 0;
+    CU(awi::launch_decode(P, c->dec_ws.p, c->dec_ws.bytes, d_chunk_off, c->d_err, st));
+    return true;
+}
+
+bool check_err(Ctx* c, cudaStream_t st, const char* what) {
+    CU(cudaSetDevice(c->dev));
+    CU(cudaStreamSynchronize(st));
+    unsigned int e = 0;
+    CU(cudaMemcpy(&e, c->d_err, 4, cudaMemcpyDeviceToHost));
+    if (e) {
+        CU(cudaMemset(c->d_err, 0, 4));
+        return fail("%s: device reported%s%s%s", what, (e & 1) ? " [payload buffer too small]" : "",
+                    (e & 2) ? " [malformed stream: chunk boundaries]" : "", (e & 4) ? " [malformed stream: chunk body]" : "");
+    }
+    return true;
+}
+
+// rows of stripe g of G over mbh macroblock rows
+inline void stripe_rows(int mbh, int g, int G, int& r0, int& r1) {
+    r0 = (int) ((long long) mbh * g / G);
+    r1 = (int) ((long long) mbh * (g + 1) / G);
+}
+
+}  // namespace
+
+// ================================================================== C ABI
+extern "C" {
+
+int gpu_codec_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+bool gpu_codec_init_devices(const int* ids, int n) {
+    std::lock_guard<std::mutex> lk(g_mu);
+    if (!g_ctx.empty()) return fail("already initialised (call gpu_codec_shutdown first)");
+    int have = gpu_codec_device_count();
+    if (have == 0) return fail("no CUDA device available; this library has no CPU path");
+    if (n <= 0 || !ids) return fail("init: need at least one device");
+    for (int i = 0; i < n; i++) {
+        if (ids[i] < 0 || ids[i] >= have) { return fail("init: device %d not present (%d visible)", ids[i], have); }
+        cudaDeviceProp prop;
+        CU(cudaGetDeviceProperties(&prop, ids[i]));
+        if (prop.major != 10) return fail("init: device %d is sm_%d%d; this library is built for sm_100a only", ids[i], prop.major, prop.minor);
+    }
+    for (int i = 0; i < n; i++) {
+        Ctx* c = new Ctx();
+        c->dev = ids[i];
+        g_ctx.push_back(c);
+        if (cudaSetDevice(c->dev) != cudaSuccess || cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess ||
+            cudaMalloc(&c->d_err, 4) != cudaSuccess || cudaMemset(c->d_err, 0, 4) != cudaSuccess ||
+            cudaMallocHost(&c->h_len, 64) != cudaSuccess) {
+            cudaError_t e = cudaGetLastError();
+            for (Ctx* k : g_ctx) destroy_ctx(k);
+            g_ctx.clear();
+            return fail("init: context creation on device %d failed: %s", ids[i], cudaGetErrorString(e));
+        }
+    }
+    return true;
+}
+
+bool gpu_codec_init(int n_gpus) {
+    if (n_gpus <= 0) return fail("init: n_gpus must be positive");
+    std::vector<int> ids(n_gpus);
+    for (int i = 0; i < n_gpus; i++) ids[i] = i;
+    return gpu_codec_init_devices(ids.data(), n_gpus);
+}
+
+void gpu_codec_shutdown(void) {
+    std::lock_guard<std::mutex> lk(g_mu);
+    for (Ctx* c : g_ctx) destroy_ctx(c);
+    g_ctx.clear();
+}
+
+const char* gpu_codec_last_error(void) { return g_last_error.c_str(); }
+
+size_t gpu_codec_max_payload_bytes(int width, int height) {
+    if (width <= 0 || height <= 0) return 0;
+    return (size_t) ((width + 15) / 16) * (size_t) ((height + 15) / 16) * 6 * 121;
+}
+
+void* gpu_codec_host_alloc(size_t bytes) {
+    void* p = nullptr;
+    if (cudaMallocHost(&p, bytes) != cudaSuccess) { cudaGetLastError(); fail("host_alloc(%zu) failed", bytes); return nullptr; }
+    return p;
+}
+void gpu_codec_host_free(void* p) { if (p) cudaFreeHost(p); }
+void gpu_codec_free(void* p) { free(p); }
+
+// ------------------------------------------------------------------ device-resident
+
+bool gpu_codec_encode_bgr_dev(int ctx, const uint8_t* d_rows, int width, int height, long long row_stride,
+                              int window_y0, int window_y1, int mb_row0, int mb_row1, uint8_t* d_payload,
+                              size_t payload_cap, uint64_t* d_payload_len, uint32_t* d_chunk_off, int8_t* d_qcoef,
+                              void* stream) {
+    Ctx* c = get_ctx(ctx);
+    if (!c) return false;
+    cudaStream_t st = stream ? (cudaStream_t) stream : c->stream;
+    return encode_dev_impl(c, d_rows, width, height, row_stride, window_y0, window_y1, mb_row0, mb_row1, d_payload,
+                           payload_cap, d_payload_len, d_chunk_off, d_qcoef, st);
+}
+
+bool gpu_codec_decode_dev(int ctx, const uint8_t* d_payload, size_t len, int width, int height, int mb_row0,
+                          int mb_row1, uint8_t* d_dst, long long row_stride, int rgb_topdown,
+                          const uint32_t* d_chunk_off, void* stream) {
+    Ctx* c = get_ctx(ctx);
+    if (!c) return false;
+    cudaStream_t st = stream ? (cudaStream_t) stream : c->stream;
+    return decode_dev_impl(c, d_payload, len, width, height, mb_row0, mb_row1, d_dst, row_stride, rgb_topdown,
+                           d_chunk_off, st);
+}
+
+bool gpu_codec_sync_check(int ctx, void* stream) {
+    Ctx* c = get_ctx(ctx);
+    if (!c) return false;
+    return check_err(c, stream ? (cudaStream_t) stream : c->stream, "sync_check");
+}
+
+bool gpu_codec_synth_bgr_dev(int ctx, uint8_t* d_rows, int width, int height, long long row_stride, int kind,
+                             uint32_t seed, int frame, void* stream) {
+    Ctx* c = get_ctx(ctx);
+    if (!c) return false;
+    if (width <= 0 || height <= 0 || row_stride < 3ll * width || kind < 0 || kind > 2) return fail("synth: bad arguments");
+    CU(cudaSetDevice(c->dev));
+    cudaStream_t st = stream ? (cudaStream_t) stream : c->stream;
+    synth_kernel<<<148 * 16, 256, 0, st>>>(d_rows, width, height, row_stride, kind, seed, frame);
+    if (row_stride > 3ll * width) pad_zero_kernel<<<148, 256, 0, st>>>(d_rows, width, height, row_stride);
+    CU(cudaGetLastError());
+    return true;
+}
+
+bool gpu_codec_selftest_colour_dev(int ctx, const uint8_t* d_in, size_t n, int inverse, uint8_t* d_out, void* stream) {
+    Ctx* c = get_ctx(ctx);
+    if (!c) return false;
+    CU(cudaSetDevice(c->dev));
+    cudaStream_t st = stream ? (cudaStream_t) stream : c->stream;
+    colour_kernel<<<148 * 8, 256, 0, st>>>(d_in, n, inverse, d_out);
+    CU(cudaGetLastError());
+    return true;
+}
+
+// ------------------------------------------------------------------ host-buffer paths
+
+bool gpu_codec_encode_bgr(const uint8_t* bmp_rows, int width, int height, int row_stride, uint8_t** payload,
+                          size_t* payload_len) {
+    if (!payload || !payload_len) return fail("encode: null output argument");
+    *payload = nullptr;
+    *payload_len = 0;
+    if (g_ctx.empty()) return fail("encode: not initialised (call gpu_codec_init)");
+    if (!bmp_rows || width <= 0 || height <= 0 || row_stride < 3 * width) return fail("encode: bad arguments");
+    const int mbw = (width + 15) / 16, mbh = (height + 15) / 16;
+    const int G = (int) g_ctx.size() < mbh ? (int) g_ctx.size() : mbh;
+    std::vector<std::unique_lock<std::mutex>> locks;
+    for (int g = 0; g < G; g++) locks.emplace_back(g_ctx[g]->mu);
+
+    // phase 1: every GPU gets its stripe (+ the macroblock row above it), encodes it
+    for (int g = 0; g < G; g++) {
+        Ctx* c = g_ctx[g];
+        int r0, r1;
+        stripe_rows(mbh, g, G, r0, r1);
+        const int y_lo = r0 > 0 ? 16 * r0 - 16 : 0, y_hi = 16 * r1 < height ? 16 * r1 : height;
+        const size_t in_bytes = (size_t) (y_hi - y_lo) * row_stride;
+        const size_t cap = (size_t) (r1 - r0) * mbw * 6 * 121 + 16;
+        CU(cudaSetDevice(c->dev));
+        if (!ensure(c->in, in_bytes) || !ensure(c->out, cap)) return false;
+        CU(cudaMemcpyAsync(c->in.p, bmp_rows + (size_t) (height - y_hi) * row_stride, in_bytes, cudaMemcpyHostToDevice, c->stream));
+        if (!encode_dev_impl(c, c->in.p, width, height, row_stride, y_lo, y_hi, r0, r1, c->out.p, cap, nullptr, nullptr,
+                             nullptr, c->stream))
+            return false;
+        CU(cudaMemcpyAsync(c->h_len, c->enc_ws.p, 8, cudaMemcpyDeviceToHost, c->stream));
+    }
+    // phase 2: exclusive prefix sum of the per-stripe byte lengths, stitch (byte seams)
+    size_t total = 0;
+    std::vector<size_t> off(G), len(G);
+    for (int g = 0; g < G; g++) {
+        if (!check_err(g_ctx[g], g_ctx[g]->stream, "encode")) return false;
+        off[g] = total;
+        len[g] = (size_t) *g_ctx[g]->h_len;
+        total += len[g];
+    }
+    uint8_t* buf = static_cast<uint8_t*>(malloc(total ? total : 1));
+    if (!buf) return fail("encode: out of host memory (%zu bytes)", total);
+    for (int g = 0; g < G; g++) {
+        Ctx* c = g_ctx[g];
+        cudaSetDevice(c->dev);
+        cudaError_t e = cudaMemcpyAsync(buf + off[g], c->out.p, len[g], cudaMemcpyDeviceToHost, c->stream);
+        if (e != cudaSuccess) { free(buf); return fail("encode: D2H failed: %s", cudaGetErrorString(e)); }
+    }
+    for (int g = 0; g < G; g++) {
+        cudaSetDevice(g_ctx[g]->dev);
+        cudaError_t e = cudaStreamSynchronize(g_ctx[g]->stream);
+        if (e != cudaSuccess) { free(buf); return fail("encode: sync failed: %s", cudaGetErrorString(e)); }
+    }
+    *payload = buf;
+    *payload_len = total;
+    return true;
+}
+
+bool gpu_codec_encode_batch_bgr(const uint8_t* const* frames, int n_frames, int width, int height, int row_stride,
+                                uint8_t** payloads, size_t* payload_lens) {
+    if (g_ctx.empty()) return fail("encode_batch: not initialised (call gpu_codec_init)");
+    if (!frames || !payloads || !payload_lens || n_frames < 0 || width <= 0 || height <= 0 || row_stride < 3 * width)
+        return fail("encode_batch: bad arguments");
+    for (int i = 0; i < n_frames; i++) { payloads[i] = nullptr; payload_lens[i] = 0; }
+    const int G = (int) g_ctx.size();
+    const int mbw = (width + 15) / 16, mbh = (height + 15) / 16;
+    const size_t in_bytes = (size_t) height * row_stride, cap = (size_t) mbw * mbh * 6 * 121 + 16;
+    std::vector<std::string> errs(G);
+    std::vector<std::thread> workers;
+    for (int g = 0; g < G; g++) {
+        workers.emplace_back([&, g]() {
+            Ctx* c = g_ctx[g];
+            std::lock_guard<std::mutex> lk(c->mu);
+            auto body = [&]() -> bool {
+                CU(cudaSetDevice(c->dev));
+                if (!ensure(c->in, in_bytes) || !ensure(c->out, cap)) return false;
+                for (int i = g; i < n_frames; i += G) {
+                    CU(cudaMemcpyAsync(c->in.p, frames[i], in_bytes, cudaMemcpyHostToDevice, c->stream));
+                    if (!encode_dev_impl(c, c->in.p, width, height, row_stride, 0, height, 0, mbh, c->out.p, cap, nullptr,
+                                         nullptr, nullptr, c->stream))
+                        return false;
+                    CU(cudaMemcpyAsync(c->h_len, c->enc_ws.p, 8, cudaMemcpyDeviceToHost, c->stream));
+                    if (!check_err(c, c->stream, "encode_batch")) return false;
+                    size_t n = (size_t) *c->h_len;
+                    payloads[i] = static_cast<uint8_t*>(malloc(n ? n : 1));
+                    if (!payloads[i]) return fail("encode_batch: out of host memory");
+                    payload_lens[i] = n;
+                    CU(cudaMemcpyAsync(payloads[i], c->out.p, n, cudaMemcpyDeviceToHost, c->stream));
+                    CU(cudaStreamSynchronize(c->stream));
+                }
+                return true;
+            };
+            if (!body()) errs[g] = g_last_error;
+        });
+    }
+    for (auto& t : workers) t.join();
+    for (int g = 0; g < G; g++)
+        if (!errs[g].empty()) {
+            for (int i = 0; i < n_frames; i++) { free(payloads[i]); payloads[i] = nullptr; payload_lens[i] = 0; }
+            return fail("%s", errs[g].c_str());
+        }
+    return true;
+}
+
+static bool decode_host(const uint8_t* payload, size_t len, int width, int height, uint8_t* dst, long long stride, int rgb) {
+    if (g_ctx.empty()) return fail("decode: not initialised (call gpu_codec_init)");
+    if (!payload || !dst || width <= 0 || height <= 0) return fail("decode: bad arguments");
+    const int mbh = (height + 15) / 16;
+    const int G = (int) g_ctx.size() < mbh ? (int) g_ctx.size() : mbh;
+    const long long pitch = rgb ? 3ll * width : stride;
+    std::vector<std::unique_lock<std::mutex>> locks;
+    for (int g = 0; g < G; g++) locks.emplace_back(g_ctx[g]->mu);
+    for (int g = 0; g < G; g++) {
+        Ctx* c = g_ctx[g];
+        int r0, r1;
+        stripe_rows(mbh, g, G, r0, r1);
+        const int y_lo = 16 * r0, y_hi = 16 * r1 < height ? 16 * r1 : height;
+        const size_t out_bytes = (size_t) (y_hi - y_lo) * pitch;
+        CU(cudaSetDevice(c->dev));
+        if (!ensure(c->in, len + 16) || !ensure(c->out, out_bytes)) return false;
+        CU(cudaMemcpyAsync(c->in.p, payload, len, cudaMemcpyHostToDevice, c->stream));
+        // the stripe's rows are contiguous in both sinks; hand the kernel the address the
+        // full frame's first byte would have
+        uint8_t* vbase = rgb ? c->out.p - (long long) y_lo * pitch : c->out.p - (long long) (height - y_hi) * pitch;
+        if (!decode_dev_impl(c, c->in.p, len, width, height, r0, r1, vbase, pitch, rgb, nullptr, c->stream)) return false;
+        uint8_t* hdst = rgb ? dst + (size_t) y_lo * pitch : dst + (size_t) (height - y_hi) * pitch;
+        if (pitch == 3ll * width) {
+            CU(cudaMemcpyAsync(hdst, c->out.p, out_bytes, cudaMemcpyDeviceToHost, c->stream));
+        } else {   // leave the caller's row padding bytes alone
+            CU(cudaMemcpy2DAsync(hdst, (size_t) pitch, c->out.p, (size_t) pitch, (size_t) 3 * width, (size_t) (y_hi - y_lo),
+                                 cudaMemcpyDeviceToHost, c->stream));
+        }
+    }
+    for (int g = 0; g < G; g++)
+        if (!check_err(g_ctx[g], g_ctx[g]->stream, "decode")) return false;
+    return true;
+}
+
+bool gpu_codec_decode_to_bgr(const uint8_t* payload, size_t len, int width, int height, uint8_t* bmp_rows, int row_stride) {
+    if (row_stride < 3 * width) return fail("decode: row_stride %d < 3*width", row_stride);
+    return decode_host(payload, len, width, height, bmp_rows, row_stride, 0);
+}
+
+bool gpu_codec_decode_to_rgb24(const uint8_t* payload, size_t len, int width, int height, uint8_t* rgb_topdown) {
+    return decode_host(payload, len, width, height, rgb_topdown, 3ll * width, 1);
+}
+
+}  // extern "C"

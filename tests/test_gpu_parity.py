@@ -1,0 +1,203 @@
+"""GPU (-m gpu): the CUDA path, called through the C ABI, against the oracle and the
+committed reference vectors.  Bit-exact everywhere: payload bytes, quantised coefficients,
+chunk offsets, decoded pixels."""
+import hashlib
+import os
+
+import numpy as np
+import pytest
+
+from conftest import golden_frames
+from image_compression_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+KIND = {"noise": 0, "photo": 1, "flat": 2}
+
+
+def sha(b):
+    return hashlib.sha256(bytes(b)).hexdigest()
+
+
+def _dev_encode(gpu, rows_t, w, h, stride, mb_rows=None, window=None, want_coefs=False):
+    import torch
+    mbw, mbh = (w + 15) // 16, (h + 15) // 16
+    r0, r1 = mb_rows or (0, mbh)
+    nch = (r1 - r0) * mbw * 6
+    payload = torch.empty(nch * 121 + 16, dtype=torch.uint8, device="cuda")
+    ln = torch.zeros(1, dtype=torch.int64, device="cuda")
+    off = torch.empty(nch, dtype=torch.int32, device="cuda")
+    q = torch.empty((nch, 64), dtype=torch.int8, device="cuda") if want_coefs else None
+    gpu.encode_dev(0, rows_t, w, h, stride, payload, ln, window=window, mb_rows=mb_rows, chunk_off=off, qcoef=q)
+    gpu.sync_check(0)
+    n = int(ln.item())
+    return payload[:n].cpu().numpy(), off.cpu().numpy().view(np.uint32), (q.cpu().numpy() if want_coefs else None)
+
+
+def test_golden_vectors_host_api(gpu, golden):
+    """Committed outputs of the reference itself."""
+    for i, kind, w, h, rows in golden_frames(golden):
+        stride = synth.bmp_stride(w)
+        payload = gpu.encode_bgr(rows, w, h, stride)
+        assert payload == golden[f"payload_{i}"].tobytes(), (kind, w, h)
+        bgr = gpu.decode_to_bgr(payload, w, h, stride)
+        assert bgr.tobytes() == golden[f"bgr_{i}"].tobytes(), (kind, w, h)
+        rgb = gpu.decode_to_rgb24(payload, w, h)
+        want = golden[f"bgr_{i}"].reshape(h, -1)[::-1, :3 * w].reshape(h, w, 3)[..., ::-1]
+        assert rgb.tobytes() == want.tobytes()
+    for line in golden["hashes"]:
+        kind, w, h, seed, frame, n, hp, hb = str(line).split(",")
+        w, h = int(w), int(h)
+        rows = synth.frame_bgr_bottomup(kind, w, h, int(seed), int(frame))
+        payload = gpu.encode_bgr(rows, w, h, synth.bmp_stride(w))
+        assert len(payload) == int(n) and sha(payload) == hp, (kind, w, h)
+        assert sha(gpu.decode_to_bgr(payload, w, h)) == hb
+
+
+@pytest.mark.parametrize("kind", ["noise", "photo", "flat"])
+@pytest.mark.parametrize("size", [(1, 1), (16, 16), (17, 15), (5, 3), (33, 47), (512, 16), (513, 17), (528, 48),
+                                  (1000, 37), (250, 130)])
+def test_encode_decode_vs_oracle(gpu, port, kind, size):
+    w, h = size
+    stride = synth.bmp_stride(w)
+    rows = synth.frame_bgr_bottomup(kind, w, h, 0xA11CE00 + w)
+    want, wq, wlen = port.encode_bgr(rows, w, h, stride, want_coefs=True)
+    got = gpu.encode_bgr(rows, w, h, stride)
+    assert got == want.tobytes()
+    import torch
+    p, off, q = _dev_encode(gpu, torch.from_numpy(rows.reshape(-1)).cuda(), w, h, stride, want_coefs=True)
+    assert (q == wq).all()
+    assert p.tobytes() == want.tobytes()
+    assert (off == np.concatenate([[0], np.cumsum(wlen)[:-1]])).all()
+    bgr, used = port.decode(want, w, h)
+    assert gpu.decode_to_bgr(got, w, h, stride).tobytes() == bgr.tobytes()
+    assert gpu.decode_to_rgb24(got, w, h).tobytes() == port.decode(want, w, h, rgb_topdown=True)[0].tobytes()
+
+
+def test_unaligned_strides_and_bases(gpu, port):
+    """Row strides that are not multiples of 16 / 4 and odd base addresses take the narrower load paths."""
+    import torch
+    w, h = 100, 40
+    rgb = synth.frame_rgb_topdown("photo", w, h, 77)
+    for stride, shift in ((300, 0), (304, 0), (301, 0), (303, 1), (320, 3)):
+        rows = np.zeros((h, stride), np.uint8)
+        rows[:, :3 * w] = rgb[::-1, :, ::-1].reshape(h, 3 * w)
+        want = port.encode_bgr(rows, w, h, stride)
+        buf = torch.zeros(h * stride + 64, dtype=torch.uint8, device="cuda")
+        buf[shift:shift + h * stride] = torch.from_numpy(rows.reshape(-1)).cuda()
+        p, _, _ = _dev_encode(gpu, buf[shift:], w, h, stride)
+        assert p.tobytes() == want.tobytes(), (stride, shift)
+        assert gpu.encode_bgr(rows, w, h, stride) == want.tobytes()
+
+
+def test_stripes_are_byte_identical(gpu, port):
+    """1/2/4/8-way macroblock-row stripes (each given only its window
+    of rows + 16 rows of halo) concatenate to the 1-way payload."""
+    import torch
+    from image_compression_b200 import stripes
+    w, h = 720, 300
+    stride = synth.bmp_stride(w)
+    rows = synth.frame_bgr_bottomup("photo", w, h, 0xA11CE03)
+    full = gpu.encode_bgr(rows, w, h, stride)
+    assert full == port.encode_bgr(rows, w, h, stride).tobytes()
+    flat = rows.reshape(-1)
+    mbh = (h + 15) // 16
+    for n in (2, 4, 8, mbh):
+        parts = []
+        for r0, r1 in stripes.stripe_rows(mbh, n):
+            y0, y1 = stripes.stripe_window(h, r0, r1)
+            b0, b1 = stripes.window_byte_range(h, stride, y0, y1)
+            win = torch.from_numpy(flat[b0:b1].copy()).cuda()
+            p, _, _ = _dev_encode(gpu, win, w, h, stride, mb_rows=(r0, r1), window=(y0, y1))
+            parts.append(p.tobytes())
+        assert stripes.stitch(parts) == full, n
+
+
+def test_batch_api(gpu, port):
+    w, h = 192, 108
+    stride = synth.bmp_stride(w)
+    frames = [synth.frame_bgr_bottomup("photo", w, h, 0xA11CE04, f) for f in range(5)]
+    got = gpu.encode_batch_bgr(frames, w, h, stride)
+    for f, g in zip(frames, got):
+        assert g == port.encode_bgr(f, w, h, stride).tobytes()
+
+
+def test_decode_modes_agree(gpu, port):
+    """Stand-alone boundary discovery == encoder side-info == oracle, and sharded reconstruct."""
+    import torch
+    for kind, w, h in (("noise", 300, 200), ("photo", 640, 427), ("flat", 64, 64), ("noise", 2100, 50)):
+        stride = synth.bmp_stride(w)
+        rows = synth.frame_bgr_bottomup(kind, w, h, 0xA11CE05)
+        rows_t = torch.from_numpy(rows.reshape(-1)).cuda()
+        p, off, _ = _dev_encode(gpu, rows_t, w, h, stride)
+        want, used, woff = port.decode(p, w, h, want_offsets=True)
+        assert used == p.size and (off == woff).all()
+        pt = torch.from_numpy(p).cuda()
+        mbh = (h + 15) // 16
+        for side in (None, torch.from_numpy(off.view(np.int32)).cuda()):
+            dst = torch.zeros(stride * h, dtype=torch.uint8, device="cuda")
+            gpu.decode_dev(0, pt, p.size, w, h, dst, stride, chunk_off=side)
+            gpu.sync_check(0)
+            assert dst.cpu().numpy().tobytes() == want.tobytes(), (kind, side is None)
+        dst = torch.zeros(stride * h, dtype=torch.uint8, device="cuda")
+        for r0, r1 in ((0, mbh // 2), (mbh // 2, mbh)):
+            gpu.decode_dev(0, pt, p.size, w, h, dst, stride, mb_rows=(r0, r1))
+        gpu.sync_check(0)
+        assert dst.cpu().numpy().tobytes() == want.tobytes()
+
+
+def test_malformed_streams_are_rejected(gpu):
+    from image_compression_b200 import codec
+    w, h = 64, 32
+    rows = synth.frame_bgr_bottomup("noise", w, h, 1)
+    p = np.frombuffer(gpu.encode_bgr(rows, w, h, synth.bmp_stride(w)), np.uint8).copy()
+    with pytest.raises(codec.GpuCodecError):
+        gpu.decode_to_bgr(p[: len(p) // 2], w, h)          # truncated
+    bad = p.copy()
+    bad[2::3] = 0xFF                                          # no EOBs where they should be
+    with pytest.raises(codec.GpuCodecError):
+        gpu.decode_to_bgr(bad, w, h)
+    with pytest.raises(codec.GpuCodecError):
+        gpu.decode_to_bgr(p, w * 2, h)                        # wrong geometry
+    assert gpu.decode_to_bgr(p, w, h) is not None             # the context recovers
+
+
+def test_colour_exhaustive_on_device(gpu, golden):
+    import torch
+    a = torch.arange(256, dtype=torch.uint8, device="cuda")
+    cube = torch.stack(torch.meshgrid(a, a, a, indexing="ij"), -1).reshape(-1, 3).contiguous()
+    out = torch.empty_like(cube)
+    for inverse in (False, True):
+        gpu.selftest_colour_dev(0, cube, inverse, out)
+        gpu.sync_check(0)
+        assert sha(out.cpu().numpy()) == str(golden["colour_cube_sha"][1 if inverse else 0])
+
+
+def test_synth_kernel_matches_numpy(gpu):
+    import torch
+    for kind in ("noise", "photo", "flat"):
+        for w, h, frame in ((37, 21, 0), (256, 64, 5)):
+            stride = synth.bmp_stride(w)
+            t = torch.full((h * stride,), 7, dtype=torch.uint8, device="cuda")
+            gpu.synth_dev(0, t, w, h, stride, KIND[kind], 0xA11CE02, frame)
+            gpu.sync_check(0)
+            assert t.cpu().numpy().tobytes() == synth.frame_bgr_bottomup(kind, w, h, 0xA11CE02, frame).tobytes()
+
+
+def test_sample1_if_present(gpu, golden):
+    local = os.path.join(os.path.dirname(__file__), "golden", "_local", "sample1.bmp")
+    path = "/root/reference/sample/sample1.bmp" if os.path.exists("/root/reference/sample/sample1.bmp") else local
+    if not os.path.exists(path):
+        pytest.skip("reference sample image not on this machine")
+    import io
+    from image_compression_b200 import awi, bmp
+    out = io.BytesIO()
+    assert awi.compress_to_awi(bmp.BMPPixelInput(open(path, "rb")), awi.AWIFileOutput(out))
+    n, h_awi, h_bmp, _ = [str(x) for x in golden["sample1"]]
+    assert len(out.getvalue()) == int(n) and sha(out.getvalue()) == h_awi
+    back = io.BytesIO()
+    assert awi.decompress_awi(awi.AWIFileInput(io.BytesIO(out.getvalue())), bmp.BMPPixelOutput(back))
+    assert sha(back.getvalue()) == h_bmp
+    sink = bmp.RGBPixelOutput()
+    assert awi.decompress_awi(awi.AWIFileInput(io.BytesIO(out.getvalue())), sink)
+    assert sink.pixels.shape == (427, 640, 3)

@@ -1,0 +1,134 @@
+"""CPU: the arithmetic the CUDA kernels run (csrc/codec_math.cuh compiled for the host by
+tests/emul) against the oracle.  This is where the exactness scheme is proven without a GPU:
+the fast AAN path may only differ from the reference where it raised an ambiguity flag."""
+import ctypes as C
+
+import numpy as np
+
+u8p = C.POINTER(C.c_uint8)
+i32p = C.POINTER(C.c_int)
+
+
+def _blocks_adversarial():
+    yy, xx = np.mgrid[0:8, 0:8]
+    out = []
+    for u in range(8):
+        for v in range(8):
+            pat = np.sign(np.cos((2 * yy + 1) * u * np.pi / 16) * np.cos((2 * xx + 1) * v * np.pi / 16))
+            for lo, hi in ((0, 255), (1, 254), (127, 129), (0, 128), (128, 255), (100, 156)):
+                out.append(np.where(pat > 0, hi, lo).ravel())
+                out.append(np.where(pat > 0, lo, hi).ravel())
+    for v in range(256):
+        out.append(np.full(64, v))
+    return np.array(out, np.uint8)
+
+
+def _transform(emul, blocks, chroma):
+    blocks = np.ascontiguousarray(blocks, np.uint8)
+    out = np.empty((len(blocks), 64), np.int32)
+    n = emul.emul_transform_n(blocks.ctypes.data_as(u8p), C.c_long(len(blocks)), chroma, out.ctypes.data_as(i32p))
+    return out, n
+
+
+def test_transform_bit_exact(emul, port):
+    rng = np.random.default_rng(11)
+    yy, xx = np.mgrid[0:8, 0:8]
+    smooth = []
+    for _ in range(4000):
+        a, b = rng.uniform(-12, 12, 2)
+        smooth.append(np.clip(rng.uniform(0, 255) + a * xx + b * yy + rng.integers(-3, 4, (8, 8)), 0, 255).ravel())
+    sets = {"noise": rng.integers(0, 256, (4000, 64)), "smooth": np.array(smooth), "adversarial": _blocks_adversarial(),
+            "near-flat": np.clip(rng.normal(128, 2, (2000, 64)), 0, 255)}
+    for name, blocks in sets.items():
+        blocks = blocks.astype(np.uint8)
+        for chroma in (0, 1):
+            got, n_exact = _transform(emul, blocks, chroma)
+            want = np.stack([port.transform(b, chroma) for b in blocks])
+            assert (got == want).all(), (name, chroma)
+            # the fallback must stay rare or the fast path is pointless
+            assert n_exact <= 0.002 * blocks.size, (name, chroma, n_exact)
+
+
+def test_fast_path_only_differs_where_flagged(emul, port):
+    rng = np.random.default_rng(12)
+    blocks = rng.integers(0, 256, (3000, 64)).astype(np.uint8)
+    from oracle import port as _p
+    _, _, scan = _p().tables()
+    for chroma in (0, 1):
+        for b in blocks:
+            chunk = np.empty(64, np.int32)
+            amb = C.c_uint64()
+            emul.emul_fast_only(b.ctypes.data_as(u8p), chroma, chunk.ctypes.data_as(i32p), C.byref(amb))
+            want = port.transform(b, chroma)
+            bad = np.nonzero(chunk != want)[0]
+            for i in bad:
+                assert (amb.value >> int(scan[i])) & 1, "unflagged fast-path mismatch"
+                assert abs(int(chunk[i]) - int(want[i])) == 1
+
+
+def test_dc_formula_exhaustive(emul, port):
+    """Every block sum S in [-8192, 8128]: integer DC == dct_block's DC, both tables."""
+    ql, qc, _ = port.tables()
+    for S in range(-8192, 8129):
+        # a block with that sum: fill with floor, distribute the remainder
+        base, rem = divmod(S + 128 * 64, 64)
+        blk = np.full(64, base, np.int64)
+        blk[:rem] += 1
+        if blk.min() < 0 or blk.max() > 255:
+            continue
+        if S % 97 and abs(S) > 64:      # full pipeline on a thinned set, the closed form on all
+            continue
+        c = port.fdct(blk.astype(np.uint8))[0]
+        for chroma, Q in ((0, ql[0]), (1, qc[0])):
+            coef = np.zeros(64, np.int32)
+            coef[0] = c
+            assert emul.emul_dc_from_sum(S, chroma) == port.quant(coef, chroma)[0], S
+
+
+def test_quant_int_matches_reference_rounding(emul, port):
+    ql, qc, _ = port.tables()
+    for chroma, tab in ((0, ql), (1, qc)):
+        for c in range(-1100, 1101):
+            want = port.quant(np.full(64, c, np.int32), chroma)
+            got = np.array([emul.emul_quant_int(c, int(q)) for q in tab])
+            assert (got == want).all(), c
+
+
+def test_rle_matches(emul, port, golden):
+    rng = np.random.default_rng(13)
+    chunks = [c.astype(np.int32) for c in golden["kat_chunk_luma"]]
+    for _ in range(500):   # sparse, dense, long zero runs, extreme magnitudes
+        c = np.zeros(64, np.int32)
+        k = rng.integers(0, 64)
+        idx = rng.choice(63, k, replace=False) + 1
+        c[idx] = rng.integers(-95, 96, k)
+        c[0] = rng.integers(-64, 65)
+        chunks.append(c)
+    c = np.zeros(64, np.int32); c[63] = 1; chunks.append(c.copy())           # 3 ZRLs then a value
+    c = np.zeros(64, np.int32); c[17] = -1; c[34] = 1; c[51] = -95; chunks.append(c.copy())
+    c = np.full(64, 95, np.int32); c[0] = 64; chunks.append(c.copy())           # longest chunk: 121 bytes
+    c = np.full(64, -95, np.int32); c[0] = -64; chunks.append(c.copy())
+    out = np.empty(256, np.uint8)
+    for c in chunks:
+        for prev in (0, int(rng.integers(-64, 65)), 64, -64):
+            c = np.ascontiguousarray(c, np.int32)
+            n = emul.emul_rle(c.ctypes.data_as(i32p), prev, out.ctypes.data_as(u8p))
+            assert out[:n].tobytes() == port.rle(c, prev), (c, prev)
+    assert len(port.rle(np.array([64] + [95] * 63, np.int32), -64)) == 121
+
+
+def test_colour_exhaustive(emul, port):
+    """All 2^24 inputs, forward and inverse."""
+    a = np.arange(256, dtype=np.uint8)
+    cube = np.ascontiguousarray(np.stack(np.meshgrid(a, a, a, indexing="ij"), -1).reshape(-1, 3))
+    out = np.empty_like(cube)
+    emul.emul_rgb2ycc_n(cube.ctypes.data_as(u8p), C.c_long(len(cube)), out.ctypes.data_as(u8p))
+    assert (out == port.rgb2ycc(cube)).all()
+    emul.emul_ycc2rgb_n(cube.ctypes.data_as(u8p), C.c_long(len(cube)), out.ctypes.data_as(u8p))
+    assert (out == port.ycc2rgb(cube)).all()
+
+
+def test_generated_tables_match_oracle(emul, port):
+    bits = np.empty(64, np.uint32)
+    emul.emul_cos_bits(bits.ctypes.data_as(C.POINTER(C.c_uint32)))
+    assert (bits == port.cos_table().view(np.uint32).ravel()).all()
