@@ -314,7 +314,7 @@ bool gpu_codec_encode_bgr_dev(int ctx, const uint8_t* d_rows, int width, int hei
                               void* stream) {
     Ctx* c = get_ctx(ctx);
     if (!c) return false;
-    cudaStream_t st = stream ? (cudaStream_t) stream : c->stream;
+    cudaStream_t st = (cudaStream_t) stream;
     return encode_dev_impl(c, d_rows, width, height, row_stride, window_y0, window_y1, mb_row0, mb_row1, d_payload,
                            payload_cap, d_payload_len, d_chunk_off, d_qcoef, st);
 }
@@ -324,7 +324,7 @@ bool gpu_codec_decode_dev(int ctx, const uint8_t* d_payload, size_t len, int wid
                           const uint32_t* d_chunk_off, void* stream) {
     Ctx* c = get_ctx(ctx);
     if (!c) return false;
-    cudaStream_t st = stream ? (cudaStream_t) stream : c->stream;
+    cudaStream_t st = (cudaStream_t) stream;
     return decode_dev_impl(c, d_payload, len, width, height, mb_row0, mb_row1, d_dst, row_stride, rgb_topdown,
                            d_chunk_off, st);
 }
@@ -332,7 +332,7 @@ bool gpu_codec_decode_dev(int ctx, const uint8_t* d_payload, size_t len, int wid
 bool gpu_codec_sync_check(int ctx, void* stream) {
     Ctx* c = get_ctx(ctx);
     if (!c) return false;
-    return check_err(c, stream ? (cudaStream_t) stream : c->stream, "sync_check");
+    return check_err(c, (cudaStream_t) stream, "sync_check");
 }
 
 bool gpu_codec_synth_bgr_dev(int ctx, uint8_t* d_rows, int width, int height, long long row_stride, int kind,
@@ -341,7 +341,7 @@ bool gpu_codec_synth_bgr_dev(int ctx, uint8_t* d_rows, int width, int height, lo
     if (!c) return false;
     if (width <= 0 || height <= 0 || row_stride < 3ll * width || kind < 0 || kind > 2) return fail("synth: bad arguments");
     CU(cudaSetDevice(c->dev));
-    cudaStream_t st = stream ? (cudaStream_t) stream : c->stream;
+    cudaStream_t st = (cudaStream_t) stream;
     synth_kernel<<<148 * 16, 256, 0, st>>>(d_rows, width, height, row_stride, kind, seed, frame);
     if (row_stride > 3ll * width) pad_zero_kernel<<<148, 256, 0, st>>>(d_rows, width, height, row_stride);
     CU(cudaGetLastError());
@@ -352,7 +352,7 @@ bool gpu_codec_selftest_colour_dev(int ctx, const uint8_t* d_in, size_t n, int i
     Ctx* c = get_ctx(ctx);
     if (!c) return false;
     CU(cudaSetDevice(c->dev));
-    cudaStream_t st = stream ? (cudaStream_t) stream : c->stream;
+    cudaStream_t st = (cudaStream_t) stream;
     colour_kernel<<<148 * 8, 256, 0, st>>>(d_in, n, inverse, d_out);
     CU(cudaGetLastError());
     return true;

@@ -97,9 +97,10 @@ bool gpu_codec_decode_to_rgb24(const uint8_t* payload, size_t len, int width, in
 
 /* ------------------------------------------------------------------ device-resident codec
  * All pointers below are device pointers on the context's device `ctx` (index into the
- * list given to init).  Calls are asynchronous on `stream` (a cudaStream_t, NULL = the
- * context's own stream) and must be stream-ordered per context: two encodes (or two
- * decodes) of one context in flight on different streams race on its scratch. */
+ * list given to init).  Calls are asynchronous on `stream` (a cudaStream_t; NULL is the
+ * CUDA default stream, as everywhere in CUDA) and must be stream-ordered per context: two
+ * encodes (or two decodes) of one context in flight on different streams race on its
+ * scratch. */
 
 /* Encode macroblock rows [mb_row0, mb_row1) of a width x height frame.  d_rows holds
  * the frame's pixel rows window_y0 <= y < window_y1 (top-down numbering) in bottom-up
