@@ -1,0 +1,108 @@
+"""GPU (-m gpu): the C host side (host/awi_gpu.c, host/awi_cli.c) — the reference's
+compress_to_awi / decompress_awi signatures over the C ABI, driven the way the reference's
+main.c drives them, checked against the oracle."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import oracle
+from image_compression_b200 import synth
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def host():
+    from image_compression_b200 import build
+    build.build()
+    subprocess.run(["make", "-C", os.path.join(ROOT, "host")], check=True, stdout=subprocess.DEVNULL)
+    return os.path.join(ROOT, "host")
+
+
+def test_cli_convert_revert_show(host, port, tmp_path):
+    w, h = 333, 201
+    rows = synth.frame_bgr_bottomup("photo", w, h, synth.SEED_BASE + 1)
+    bmp = tmp_path / "img.bmp"
+    bmp.write_bytes(oracle.bmp_wrap(rows, w, h))
+    cli = os.path.join(host, "awi_cli")
+    r = subprocess.run([cli, "convert", str(bmp)], capture_output=True, text=True)
+    assert r.returncode == 0 and "convert completed!" in r.stdout, r.stderr
+    awi = (tmp_path / "img.awi").read_bytes()
+    want = port.encode_bgr(rows, w, h, synth.bmp_stride(w))
+    assert awi == oracle.awi_header(w, h) + want.tobytes()
+    os.remove(bmp)
+    r = subprocess.run([cli, "revert", str(tmp_path / "img.awi")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    back = (tmp_path / "img.bmp").read_bytes()
+    assert back[:54] == oracle.bmp_wrap(rows, w, h)[:54]
+    assert back[54:] == port.decode(want, w, h)[0].tobytes()
+    r = subprocess.run([cli, "show", str(tmp_path / "img.awi")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    assert (tmp_path / "img.rgb").read_bytes() == port.decode(want, w, h, rgb_topdown=True)[0].tobytes()
+    # exit codes of main.c:72-86
+    assert subprocess.run([cli, "convert", str(tmp_path / "img.awi")], capture_output=True).returncode == 2
+    assert subprocess.run([cli, "revert", str(tmp_path / "nope.awi")], capture_output=True).returncode == 1
+
+
+class Block16(C.Structure):
+    _fields_ = [("b", (C.c_uint8 * 16) * 16)]
+
+
+class RGBBlock16(C.Structure):
+    _fields_ = [("r", Block16), ("g", Block16), ("b", Block16)]
+
+
+class PixelInput(C.Structure):
+    pass
+
+
+class BitsOutput(C.Structure):
+    pass
+
+
+PixelInput._fields_ = [("context", C.c_void_p), ("width", C.c_int), ("height", C.c_int),
+                       ("begin", C.CFUNCTYPE(C.c_bool, C.POINTER(PixelInput))),
+                       ("read_block", C.CFUNCTYPE(C.c_bool, C.POINTER(PixelInput), C.c_int, C.c_int, C.POINTER(RGBBlock16))),
+                       ("end", C.CFUNCTYPE(C.c_bool, C.POINTER(PixelInput)))]
+BitsOutput._fields_ = [("context", C.c_void_p), ("buffer", C.c_uint8), ("bit_count", C.c_int),
+                       ("write", C.CFUNCTYPE(C.c_bool, C.POINTER(BitsOutput), C.c_void_p, C.c_size_t))]
+
+
+def test_compress_to_awi_through_plugin_vtables(host, port):
+    """An arbitrary PixelInput/BitsOutput pair (here: Python callbacks) like any plug-in of pixelrw.h."""
+    lib = C.CDLL(os.path.join(host, "libawi_gpu_host.so"))
+    lib.compress_to_awi.restype = C.c_bool
+    w, h = 70, 45
+    rgb = synth.frame_rgb_topdown("noise", w, h, 99)
+    order, sink = [], bytearray()
+
+    def begin(self):
+        self.contents.width, self.contents.height = w, h
+        return True
+
+    def read_block(self, bx, by, out):
+        order.append((by, bx))
+        blk = out.contents
+        for name, ch in (("r", 0), ("g", 1), ("b", 2)):
+            plane = np.zeros((16, 16), np.uint8)
+            sub = rgb[16 * by:16 * by + 16, 16 * bx:16 * bx + 16, ch]
+            plane[:sub.shape[0], :sub.shape[1]] = sub
+            C.memmove(getattr(blk, name).b, plane.ctypes.data, 256)
+        return True
+
+    def write(self, data, size):
+        sink.extend(C.string_at(data, size))
+        return True
+
+    pi = PixelInput(None, 0, 0, PixelInput._fields_[3][1](begin), PixelInput._fields_[4][1](read_block),
+                    PixelInput._fields_[5][1](0))
+    bo = BitsOutput(None, 0, 0, BitsOutput._fields_[3][1](write))
+    assert lib.compress_to_awi(C.byref(pi), C.byref(bo))
+    assert order == [(y, x) for y in range(3) for x in range(5)]            # strict raster order
+    rows = synth.rows_from_rgb_topdown(rgb)
+    want = port.encode_bgr(rows, w, h, synth.bmp_stride(w))
+    assert bytes(sink) == oracle.awi_header(w, h) + want.tobytes()
