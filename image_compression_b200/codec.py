@@ -33,6 +33,8 @@ SYMBOLS = [
     ("gpu_codec_encode_bgr_dev", C.c_bool, [C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_longlong, C.c_int, C.c_int,
                                             C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p,
                                             C.c_void_p, C.c_void_p]),
+    ("gpu_codec_encode_bgr_dev_noalloc", C.c_bool, [C.c_void_p, C.c_int, C.c_int, C.c_longlong, C.c_void_p, C.c_size_t,
+                                                    C.c_void_p, C.c_void_p, C.c_void_p]),
     ("gpu_codec_decode_dev", C.c_bool, [C.c_int, C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_int,
                                         C.c_void_p, C.c_longlong, C.c_int, C.c_void_p, C.c_void_p]),
     ("gpu_codec_sync_check", C.c_bool, [C.c_int, C.c_void_p]),
@@ -198,6 +200,14 @@ def encode_dev(ctx: int, rows, width: int, height: int, row_stride: int, payload
                                         chunk_off.data_ptr() if chunk_off is not None else None,
                                         qcoef.data_ptr() if qcoef is not None else None, _stream_ptr(stream)),
            "gpu_codec_encode_bgr_dev")
+
+
+def encode_dev_noalloc(rows, width: int, height: int, row_stride: int, payload, payload_len, status, stream=None) -> None:
+    """gpu_codec_encode_bgr_dev_noalloc: whole frame on the current device, scratch inside the library
+    (no allocation; at most 2,097,152 macroblocks). `payload_len` int64[1], `status` int32[1] tensors."""
+    _check(load().gpu_codec_encode_bgr_dev_noalloc(rows.data_ptr(), width, height, row_stride, payload.data_ptr(),
+                                                   payload.numel(), payload_len.data_ptr(), status.data_ptr(),
+                                                   _stream_ptr(stream)), "gpu_codec_encode_bgr_dev_noalloc")
 
 
 def decode_dev(ctx: int, payload, length: int, width: int, height: int, dst, row_stride: int, rgb_topdown: bool = False,

@@ -505,3 +505,85 @@ bool gpu_codec_decode_to_rgb24(const uint8_t* payload, size_t len, int width, in
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------ encode without allocating
+//
+// Some callers may not allocate device memory at the point where they encode: a frame
+// loop that has handed the whole device to its own pool, a latency-critical path that
+// cannot take the device-wide synchronisation a cudaMalloc/cudaFree implies, or code that
+// runs while some other stream is being captured into a graph (allocation calls are not
+// allowed then).  The regular device entry point grows the context's scratch with
+// cudaMalloc on demand, so it is not for them.  This variant keeps the encode kernel's
+// scratch — the tile ticket and one look-back descriptor per 32-macroblock tile — in a
+// fixed array that is part of the library image.  Every GPU that loads the library
+// carries these 512 KB + 256 B until the process exits.
+namespace {
+
+constexpr int NOALLOC_MAX_TILES = 65536;          // 2,097,152 macroblocks, e.g. up to 23168 x 23168 pixels
+constexpr size_t NOALLOC_HEADER = 256;            // [0,8) spare, [8,12) tile ticket
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_HEADER + (size_t) NOALLOC_MAX_TILES * 8];
+
+// In host code `g_noalloc_scratch` is only a handle for the runtime, not an address the
+// GPU understands; the real per-device address comes from cudaGetSymbolAddress, asked
+// once per device with that device current, and is what the kernel is given.
+constexpr int NOALLOC_MAX_DEVICES = 64;
+unsigned char* g_noalloc_ptr[NOALLOC_MAX_DEVICES] = { nullptr };
+std::mutex g_noalloc_mu;
+
+bool noalloc_scratch_for_current_device(unsigned char** out) {
+    int dev = -1;
+    CU(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= NOALLOC_MAX_DEVICES) return fail("encode_noalloc: device index %d not supported", dev);
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (!g_noalloc_ptr[dev]) {
+        void* p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (e != cudaSuccess || !p) return fail("encode_noalloc: cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
+        g_noalloc_ptr[dev] = static_cast<unsigned char*>(p);
+    }
+    *out = g_noalloc_ptr[dev];
+    return true;
+}
+
+}  // namespace
+
+extern "C" bool gpu_codec_encode_bgr_dev_noalloc(const uint8_t* d_rows, int width, int height, long long row_stride,
+                                                 uint8_t* d_payload, size_t payload_cap, uint64_t* d_payload_len,
+                                                 uint32_t* d_status, void* stream) {
+    if (width <= 0 || height <= 0) return fail("encode_noalloc: bad geometry %dx%d", width, height);
+    if (row_stride < 3ll * width) return fail("encode_noalloc: row_stride %lld < 3*width", row_stride);
+    if (!d_rows || !d_payload || !d_payload_len || !d_status) return fail("encode_noalloc: null device pointer");
+    const int mbw = (width + 15) / 16, mbh = (height + 15) / 16;
+    const long long n_mb = (long long) mbw * mbh;
+    const long long n_tiles = (n_mb + awi::ENC_TILE_MB - 1) / awi::ENC_TILE_MB;
+    if (n_tiles > NOALLOC_MAX_TILES)
+        return fail("encode_noalloc: %dx%d needs %lld tiles of %d macroblocks, the built-in scratch holds %d "
+                    "(at most %lld macroblocks per call); use gpu_codec_encode_bgr_dev for larger frames",
+                    width, height, n_tiles, awi::ENC_TILE_MB, NOALLOC_MAX_TILES, (long long) NOALLOC_MAX_TILES * awi::ENC_TILE_MB);
+    unsigned char* scratch = nullptr;
+    if (!noalloc_scratch_for_current_device(&scratch)) return false;
+    cudaStream_t st = (cudaStream_t) stream;
+    // the array still holds the previous call's ticket and descriptors: both must start at zero
+    CU(cudaMemsetAsync(scratch, 0, NOALLOC_HEADER + (size_t) n_tiles * 8, st));
+    CU(cudaMemsetAsync(d_status, 0, 4, st));
+
+    awi::EncParams P{};
+    P.rows = d_rows;
+    P.stride = row_stride;
+    P.width = width;
+    P.height = height;
+    P.align = align_of(d_rows, row_stride);
+    P.mbw = mbw;
+    P.mb0 = 0;
+    P.mb1 = (int) n_mb;
+    P.out = d_payload;
+    P.out_cap = payload_cap;
+    P.out_len = reinterpret_cast<unsigned long long*>(d_payload_len);
+    P.ticket = reinterpret_cast<unsigned int*>(scratch + 8);
+    P.desc = reinterpret_cast<unsigned long long*>(scratch + NOALLOC_HEADER);
+    P.err = d_status;
+    P.chunk_off = nullptr;
+    P.qcoef = nullptr;
+    CU(awi::launch_encode(P, (int) n_tiles, st));
+    return true;
+}

@@ -115,6 +115,29 @@ bool gpu_codec_encode_bgr_dev(int ctx, const uint8_t* d_rows, int width, int hei
                               uint8_t* d_payload, size_t payload_cap, uint64_t* d_payload_len,
                               uint32_t* d_chunk_off, int8_t* d_qcoef, void* stream);
 
+/* Whole-frame encode of device-resident rows that allocates nothing (no counterpart in
+ * the reference; it exists for callers of this library that must not allocate device
+ * memory while encoding: engines that own all device memory through their own pool,
+ * loops that cannot afford the device-wide stall of cudaMalloc/cudaFree, code running
+ * while another stream is under graph capture).  Same kernel and same bytes as
+ * gpu_codec_encode_bgr_dev on the full frame, but the kernel's scratch (tile ticket +
+ * one 8-byte descriptor per tile of 32 macroblocks) is a fixed 512 KB + 256 B array
+ * inside the library, so:
+ *   - limit: at most 65536 tiles = 2,097,152 macroblocks per call (e.g. 16384 x 16384 is
+ *     1,048,576); larger frames are refused with an error, nothing is launched;
+ *   - no context and no gpu_codec_init are needed; the frame is encoded on the CURRENT
+ *     device, all pointers are device pointers there;
+ *   - the first call on each device looks up the array's device address; make that
+ *     first call before starting any stream capture;
+ *   - all calls on one device share the array: two calls whose kernels overlap on the
+ *     GPU (different streams, no ordering) corrupt each other; order them;
+ *   - d_payload_len (8 bytes) receives the payload length, d_status (4 bytes) 0 on
+ *     success or bit 0 set when payload_cap was too small (then nothing was written).
+ *     Both are written on `stream`; read them after synchronising it. */
+bool gpu_codec_encode_bgr_dev_noalloc(const uint8_t* d_rows, int width, int height, long long row_stride,
+                                      uint8_t* d_payload, size_t payload_cap, uint64_t* d_payload_len,
+                                      uint32_t* d_status, void* stream);
+
 /* Decode a whole payload's chunk structure, reconstruct macroblock rows
  * [mb_row0, mb_row1) ("replicated parse, sharded reconstruct").  d_dst is the address
  * of bottom-up row 0 (BGR sink) or of pixel (0,0) (RGB24 sink, rgb_topdown != 0) of the
