@@ -12,8 +12,9 @@
 //   C  flagged coefficients recomputed warp-cooperatively in the reference's exact
 //      operation order
 //   D  one thread per chunk: run-length symbols + bit packing into a smem slot
-//   E  CTA scan of chunk byte lengths + decoupled look-back across tiles
-//   F  byte scatter of the slots to their final payload offsets
+//   E  CTA scan of chunk byte lengths; warp 0 resolves the tile's payload offset by
+//      decoupled look-back while the other warps compact the slots in smem
+//   F  coalesced word copy of the compacted tile to its final payload offset
 //
 // Chunks are byte aligned (rle.c:107) so the device-wide scan is over BYTE lengths.
 // The only cross-tile state, the six DC predictors (awi.c:91-92), is rebuilt from a
@@ -26,18 +27,23 @@
 
 namespace awi {
 
+#ifndef ENC_MIN_CTAS
+#define ENC_MIN_CTAS 4                           // resident CTAs per SM the register budget is sized for
+#endif
 constexpr int TILE_MB = ENC_TILE_MB;             // 32 macroblocks per tile
 constexpr int THREADS = 192;                     // one thread per 8x8 block of the tile
 constexpr int NWARPS = THREADS / 32;
 constexpr int ROW_BYTES = TILE_MB * 48;          // one pixel row of the tile in smem
 constexpr int RAW_BYTES = 16 * ROW_BYTES;        // 24576
 constexpr int SLOT = 124;                        // staging bytes per chunk (max 121), 31 words: conflict-free
+constexpr int COMPACT_CAP = THREADS * 64;        // compacted tile lives in the (dead) coefficient buffer
 static_assert(THREADS * SLOT <= RAW_BYTES, "chunk slots alias the raw tile");
+static_assert(THREADS == 2 * TILE_MB * 3, "loader: one fixed (macroblock, 16-byte piece) per thread, two rows per pass");
 
 struct __align__(16) EncSmem {
     uint8_t raw[RAW_BYTES];                      // phase A-C: pixels; phase D-F: chunk slots
     uint8_t halo[16 * 48];                       // macroblock preceding the tile
-    uint32_t coef[THREADS * 16];                 // int8[64] per block, scan order, quads swizzled
+    uint32_t coef[THREADS * 16];                 // int8[64] per block, scan order, quads swizzled; phase E-F: compacted tile
     unsigned long long amb[THREADS];             // per block: natural positions to recompute
     float cosf[64];
     int dc[(TILE_MB + 1) * 6];                   // quantised DCs, [0] = halo macroblock
@@ -45,6 +51,8 @@ struct __align__(16) EncSmem {
     uint32_t len[THREADS];                       // chunk byte lengths, chunk order
     uint32_t off[THREADS];                       // exclusive offsets inside the tile
     uint32_t warp_tot[NWARPS];
+    uint16_t amb_list[THREADS];                  // threads whose block has flagged coefficients
+    int amb_count;
     unsigned long long tile_base;
     int tile;
 };
@@ -69,70 +77,107 @@ __device__ __forceinline__ int coef_word(int tid, int word) {      // swizzled w
     return tid * 16 + ((((word >> 2) ^ (tid >> 1)) & 3) << 2) + (word & 3);
 }
 
+// Look-back descriptors carry value and state in one 64-bit word, so relaxed accesses are
+// enough (no other data is published through them) — and unlike ld.acquire they do not
+// invalidate the SM's L1 on every poll.
 __device__ __forceinline__ uint64_t ld_desc(const unsigned long long* p) {
     unsigned long long v;
-    asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
     return v;
 }
 __device__ __forceinline__ void st_desc(unsigned long long* p, unsigned long long v) {
-    asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 
 // ---------------------------------------------------------------- phase A
 // bmp.c:48-119 addressing.  Pixel bytes outside the image read as zero (bmp.c:89-93,106-109).
-__device__ __forceinline__ uint4 load_piece(const EncParams& P, int mb_global, int row, int k) {
-    int my = mb_global / P.mbw, mx = mb_global - my * P.mbw;
-    int y = my * 16 + row;
-    int xb = mx * 48 + k * 16;
+// `src` points at the piece; `valid` = bytes of it inside the image row (<= 0: none).
+__device__ __forceinline__ uint4 load_piece(const uint8_t* src, int valid, int align) {
     uint4 v = make_uint4(0, 0, 0, 0);
-    int valid = P.width * 3 - xb;                      // bytes of this piece inside the image row
-    if (y >= P.height || valid <= 0) return v;
-    const uint8_t* src = P.rows + (long long) (P.height - 1 - y) * P.stride + xb;
+    if (valid <= 0) return v;
     if (valid >= 16) {
-        if (P.align == 16) return __ldg(reinterpret_cast<const uint4*>(src));
-        if (P.align == 4) {
+        if (align == 16) return __ldg(reinterpret_cast<const uint4*>(src));
+        if (align == 4) {
             const uint32_t* s = reinterpret_cast<const uint32_t*>(src);
             return make_uint4(__ldg(s), __ldg(s + 1), __ldg(s + 2), __ldg(s + 3));
         }
         valid = 16;
     }
-    uint32_t w[4] = { 0, 0, 0, 0 };
-    for (int i = 0; i < valid; i++) w[i >> 2] |= (uint32_t) __ldg(src + i) << (8 * (i & 3));
-    return make_uint4(w[0], w[1], w[2], w[3]);
+    uint32_t w0 = 0, w1 = 0, w2 = 0, w3 = 0;
+    for (int i = 0; i < valid; i++) {
+        uint32_t b = (uint32_t) __ldg(src + i) << (8 * (i & 3));
+        if (i < 4) w0 |= b; else if (i < 8) w1 |= b; else if (i < 12) w2 |= b; else w3 |= b;
+    }
+    return make_uint4(w0, w1, w2, w3);
 }
 
 // ---------------------------------------------------------------- phase B helpers
 __device__ __forceinline__ int byte_of(uint32_t w, int i) { return (int) ((w >> (8 * i)) & 0xffu); }
 
+// The literal fp64 expressions (color.c:31-33) are needed for roughly one pixel in a
+// thousand.  Kept out of line: one copy each instead of one per unrolled pixel, which is
+// what keeps the hot loop's instruction footprint small.
+__device__ __noinline__ int luma_exact_call(int r, int g, int b) { return y_exact(r, g, b); }
+__device__ __noinline__ int chroma_exact_call(int r, int g, int b, int cr) { return cr ? cr_exact(r, g, b) : cb_exact(r, g, b); }
+
 // 8 pixels (24 bytes B,G,R,...) in 6 words -> 8 centred luma samples
 __device__ __forceinline__ void luma_row(const uint32_t* w, float* d) {
+    uint32_t zero_rem = 0;
 #pragma unroll
     for (int x = 0; x < 8; x++) {
         int b = byte_of(w[(3 * x) >> 2], (3 * x) & 3);
         int g = byte_of(w[(3 * x + 1) >> 2], (3 * x + 1) & 3);
         int r = byte_of(w[(3 * x + 2) >> 2], (3 * x + 2) & 3);
-        d[x] = centred(luma_of(r, g, b));
+        uint32_t n = (uint32_t) (299 * r + 587 * g + 114 * b);
+        uint32_t q = __umulhi(n, 4294968u);
+        zero_rem |= (n - q * 1000u == 0u) ? (1u << x) : 0u;
+        d[x] = centred((int) q);
+    }
+    if (zero_rem) {                                  // exact multiple of 1000 somewhere in the row: rare
+#pragma unroll
+        for (int x = 0; x < 8; x++) {
+            if (zero_rem & (1u << x)) {
+                int b = byte_of(w[(3 * x) >> 2], (3 * x) & 3);
+                int g = byte_of(w[(3 * x + 1) >> 2], (3 * x + 1) & 3);
+                int r = byte_of(w[(3 * x + 2) >> 2], (3 * x + 2) & 3);
+                d[x] = centred(luma_exact_call(r, g, b));
+            }
+        }
     }
 }
 
-// one colour-difference sample; cr selects the coefficient set (warp-divergent only in
-// the value of three registers, not in control flow, except for the rare exact path)
+// one colour-difference sample; cr selects the coefficient set
 __device__ __forceinline__ int chroma_of(int r, int g, int b, bool cr) {
     int kr = cr ? 5000 : -1687, kg = cr ? -4187 : -3313, kb = cr ? -813 : 5000;
     uint32_t n = (uint32_t) (kr * r + kg * g + kb * b + 1280000);
     uint32_t q = __umulhi(n, 3435974u) >> 3;
-    if (n - q * 10000u == 0u) return cr ? cr_exact(r, g, b) : cb_exact(r, g, b);
+    if (n - q * 10000u == 0u) return chroma_exact_call(r, g, b, cr ? 1 : 0);
     return (int) q;
 }
 
 // 16 pixels (48 bytes) in 12 words -> samples of the 8 even pixels (color.c:82-83)
-__device__ __forceinline__ void chroma_row(const uint32_t* w, float* d, bool cr) {
+__device__ __forceinline__ void chroma_row(const uint32_t* w, float* d, int kr, int kg, int kb, int cr) {
+    uint32_t zero_rem = 0;
 #pragma unroll
     for (int x = 0; x < 8; x++) {
         int b = byte_of(w[(6 * x) >> 2], (6 * x) & 3);
         int g = byte_of(w[(6 * x + 1) >> 2], (6 * x + 1) & 3);
         int r = byte_of(w[(6 * x + 2) >> 2], (6 * x + 2) & 3);
-        d[x] = centred(chroma_of(r, g, b, cr));
+        uint32_t n = (uint32_t) (kr * r + kg * g + kb * b + 1280000);
+        uint32_t q = __umulhi(n, 3435974u) >> 3;
+        zero_rem |= (n - q * 10000u == 0u) ? (1u << x) : 0u;
+        d[x] = centred((int) q);
+    }
+    if (zero_rem) {
+#pragma unroll
+        for (int x = 0; x < 8; x++) {
+            if (zero_rem & (1u << x)) {
+                int b = byte_of(w[(6 * x) >> 2], (6 * x) & 3);
+                int g = byte_of(w[(6 * x + 1) >> 2], (6 * x + 1) & 3);
+                int r = byte_of(w[(6 * x + 2) >> 2], (6 * x + 2) & 3);
+                d[x] = centred(chroma_exact_call(r, g, b, cr));
+            }
+        }
     }
 }
 
@@ -149,13 +194,13 @@ __device__ __forceinline__ int sample_of(const EncSmem& S, int tid, int y, int x
 }
 
 // ---------------------------------------------------------------- the kernel
-__global__ void __launch_bounds__(THREADS, 3) awi_encode_kernel(EncParams P) {
+__global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncParams P) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     EncSmem& S = *reinterpret_cast<EncSmem*>(smem_raw);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
     // ticketed tile order: a tile only ever waits on tiles whose CTAs already run
-    if (tid == 0) S.tile = (int) atomicAdd(P.ticket, 1u);
+    if (tid == 0) { S.tile = (int) atomicAdd(P.ticket, 1u); S.amb_count = 0; }
     if (tid < 64) S.cosf[tid] = __uint_as_float(cos_bits_rt(tid));
     if (tid < 6) S.halo_sum[tid] = 0;
     __syncthreads();
@@ -164,22 +209,37 @@ __global__ void __launch_bounds__(THREADS, 3) awi_encode_kernel(EncParams P) {
     const int n_mb = min(TILE_MB, P.mb1 - mb_first);
     const bool has_halo = mb_first > 0;
 
-    // ---- A: stage pixels
+    // ---- A: stage pixels.  Thread = one 16-byte piece column (macroblock m, piece k) x 8 rows.
     {
-        uint4* dst = reinterpret_cast<uint4*>(S.raw);
-        constexpr int PIECES = 16 * TILE_MB * 3;
-#pragma unroll 8
-        for (int p = tid; p < PIECES; p += THREADS) {
-            int row = p / (3 * TILE_MB), rem = p - row * (3 * TILE_MB);
-            int m = rem / 3, k = rem - 3 * m;
-            uint4 v = make_uint4(0, 0, 0, 0);
-            if (m < n_mb) v = load_piece(P, mb_first + m, row, k);
-            dst[p] = v;
+        const int col = tid % (3 * TILE_MB), m = col / 3, k = col - 3 * m;
+        const int r0 = tid / (3 * TILE_MB);                       // 0 or 1
+        uint4 v[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) v[i] = make_uint4(0, 0, 0, 0);
+        if (m < n_mb) {
+            const int g = mb_first + m;
+            const int my = g / P.mbw, mx = g - my * P.mbw;
+            const int xb = mx * 48 + k * 16;
+            const int valid = P.width * 3 - xb;
+            const int y0 = my * 16 + r0;
+            const uint8_t* src = P.rows + (long long) (P.height - 1 - y0) * P.stride + xb;
+#pragma unroll
+            for (int i = 0; i < 8; i++)
+                if (y0 + 2 * i < P.height) v[i] = load_piece(src - (long long) (2 * i) * P.stride, valid, P.align);
         }
+        uint4* dst = reinterpret_cast<uint4*>(S.raw) + r0 * (3 * TILE_MB) + col;
+#pragma unroll
+        for (int i = 0; i < 8; i++) dst[i * 2 * (3 * TILE_MB)] = v[i];
         if (tid < 48) {
-            uint4 v = make_uint4(0, 0, 0, 0);
-            if (has_halo) v = load_piece(P, mb_first - 1, tid / 3, tid % 3);
-            reinterpret_cast<uint4*>(S.halo)[tid] = v;
+            uint4 h = make_uint4(0, 0, 0, 0);
+            if (has_halo) {
+                const int g = mb_first - 1, row = tid / 3, kk = tid - 3 * row;
+                const int my = g / P.mbw, mx = g - my * P.mbw;
+                const int xb = mx * 48 + kk * 16, y = my * 16 + row;
+                if (y < P.height)
+                    h = load_piece(P.rows + (long long) (P.height - 1 - y) * P.stride + xb, P.width * 3 - xb, P.align);
+            }
+            reinterpret_cast<uint4*>(S.halo)[tid] = h;
         }
     }
     __syncthreads();
@@ -203,13 +263,14 @@ __global__ void __launch_bounds__(THREADS, 3) awi_encode_kernel(EncParams P) {
             fdct_quant_pack<false>(d, packed, amb);
         } else {
             const uint8_t* base = S.raw + me.mb * 48;
-            const bool cr = me.type == 5;
+            const int cr = me.type == 5;
+            const int kr = cr ? 5000 : -1687, kg = cr ? -4187 : -3313, kb = cr ? -813 : 5000;
 #pragma unroll
             for (int y = 0; y < 8; y++) {
                 const uint4* src = reinterpret_cast<const uint4*>(base + 2 * y * ROW_BYTES);
                 uint4 a = src[0], b = src[1], c = src[2];
                 uint32_t w[12] = { a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w, c.x, c.y, c.z, c.w };
-                chroma_row(w, d + 8 * y, cr);
+                chroma_row(w, d + 8 * y, kr, kg, kb, cr);
             }
             fdct_quant_pack<true>(d, packed, amb);
         }
@@ -219,8 +280,11 @@ __global__ void __launch_bounds__(THREADS, 3) awi_encode_kernel(EncParams P) {
             *reinterpret_cast<uint4*>(&S.coef[coef_word(tid, 4 * q4)]) = v;
         }
         S.dc[(me.mb + 1) * 6 + me.type] = (int) (int8_t) (packed[0] & 0xff);
+        if (amb != 0) {
+            S.amb[tid] = amb;
+            S.amb_list[atomicAdd(&S.amb_count, 1)] = (uint16_t) tid;
+        }
     }
-    S.amb[tid] = amb;
 
     // halo macroblock: only the six block sums are needed (integer DC formula)
     if (has_halo) {
@@ -245,32 +309,32 @@ __global__ void __launch_bounds__(THREADS, 3) awi_encode_kernel(EncParams P) {
             if (lane == 0) { atomicAdd(&S.halo_sum[4], cb); atomicAdd(&S.halo_sum[5], cr); }
         }
     }
-    const int any_amb = __syncthreads_or(amb != 0);
+    __syncthreads();
 
     if (tid < 6)
         S.dc[tid] = has_halo ? quant_int(dc_coef_from_sum(S.halo_sum[tid] - 128 * 64), tid < 4 ? 16 : 17) : 0;
 
     // ---- C: exact recomputation of flagged coefficients (dct.c:26-53 operation order)
-    if (any_amb) {
-        for (int b = warp; b < THREADS; b += NWARPS) {
-            unsigned long long m = S.amb[b];
-            const bool chroma = b >= 128;
-            while (m) {
-                int k = __ffsll((long long) m) - 1;
-                m &= m - 1;
-                int u = k >> 3, v = k & 7;
-                int y = lane >> 2, x0 = (lane & 3) * 2;
-                float cyu = S.cosf[y * 8 + u];
-                double part = (double) exact_product(sample_of(S, b, y, x0) - 128, cyu, S.cosf[x0 * 8 + v]);
-                part += (double) exact_product(sample_of(S, b, y, x0 + 1) - 128, cyu, S.cosf[(x0 + 1) * 8 + v]);
+    const int n_amb = S.amb_count;
+    for (int e = warp; e < n_amb; e += NWARPS) {
+        const int b = S.amb_list[e];
+        unsigned long long m = S.amb[b];
+        const bool chroma = b >= 128;
+        while (m) {
+            int k = __ffsll((long long) m) - 1;
+            m &= m - 1;
+            int u = k >> 3, v = k & 7;
+            int y = lane >> 2, x0 = (lane & 3) * 2;
+            float cyu = S.cosf[y * 8 + u];
+            double part = (double) exact_product(sample_of(S, b, y, x0) - 128, cyu, S.cosf[x0 * 8 + v]);
+            part += (double) exact_product(sample_of(S, b, y, x0 + 1) - 128, cyu, S.cosf[(x0 + 1) * 8 + v]);
 #pragma unroll
-                for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
-                if (lane == 0) {
-                    int c = exact_coef_finish(part, u, v);
-                    int q = quant_int(c, chroma ? qchroma_rt(k) : qluma_rt(k));
-                    int idx = unscan_rt(k);
-                    reinterpret_cast<int8_t*>(&S.coef[coef_word(b, idx >> 2)])[idx & 3] = (int8_t) q;
-                }
+            for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+            if (lane == 0) {
+                int c = exact_coef_finish(part, u, v);
+                int q = quant_int(c, chroma ? qchroma_rt(k) : qluma_rt(k));
+                int idx = unscan_rt(k);
+                reinterpret_cast<int8_t*>(&S.coef[coef_word(b, idx >> 2)])[idx & 3] = (int8_t) q;
             }
         }
     }
@@ -304,10 +368,12 @@ __global__ void __launch_bounds__(THREADS, 3) awi_encode_kernel(EncParams P) {
         int prev = S.dc[me.mb * 6 + me.type];
         my_len = (uint32_t) rle_chunk(dc, prev, ((unsigned long long) hi << 32) | lo, coef, put);
     }
-    S.len[me.mb * 6 + me.type] = my_len;
+    const int my_chunk = me.mb * 6 + me.type;
+    S.len[my_chunk] = my_len;
     __syncthreads();
 
-    // ---- E: offsets inside the tile (chunk order = tid order here), then across tiles
+    // ---- E: offsets inside the tile (chunk order = tid order here)
+    uint32_t total;
     {
         uint32_t v = S.len[tid], incl = v;
 #pragma unroll
@@ -317,57 +383,89 @@ __global__ void __launch_bounds__(THREADS, 3) awi_encode_kernel(EncParams P) {
         }
         if (lane == 31) S.warp_tot[warp] = incl;
         __syncthreads();
-        uint32_t wbase = 0, total = 0;
+        uint32_t wbase = 0;
+        total = 0;
 #pragma unroll
         for (int i = 0; i < NWARPS; i++) { uint32_t t = S.warp_tot[i]; if (i < warp) wbase += t; total += t; }
         S.off[tid] = wbase + incl - v;
-
-        if (warp == 0) {
-            constexpr unsigned long long FLAG_AGG = 1ull << 62, FLAG_PFX = 2ull << 62, VMASK = (1ull << 62) - 1;
-            unsigned long long excl = 0;
-            if (tile > 0) {
-                if (lane == 0) st_desc(P.desc + tile, FLAG_AGG | total);
-                int base = tile - 1;
-                while (true) {
-                    int idx = base - lane;
-                    unsigned long long dsc = FLAG_PFX;                // virtual prefix 0 before tile 0
-                    if (idx >= 0) { do { dsc = ld_desc(P.desc + idx); } while ((dsc >> 62) == 0); }
-                    unsigned pm = __ballot_sync(0xffffffffu, (dsc >> 62) == 2);
-                    int first = pm ? (__ffs((int) pm) - 1) : 31;
-                    unsigned long long c = lane <= first ? (dsc & VMASK) : 0ull;
-#pragma unroll
-                    for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
-                    excl += c;
-                    if (pm) break;
-                    base -= 32;
-                }
-            }
-            if (lane == 0) {
-                st_desc(P.desc + tile, FLAG_PFX | (excl + total));
-                S.tile_base = excl;
-                if (mb_first + n_mb >= P.mb1) *P.out_len = excl + total;      // last tile: payload length
-            }
-        }
     }
-    __syncthreads();
-
-    // ---- F: scatter the chunk bytes
-    {
-        const unsigned long long base = S.tile_base;
-        const int c = tid;                               // chunk index inside the tile
-        const int mb = c / 6, type = c - 6 * mb;
-        const uint32_t L = S.len[c], O = S.off[c];
-        const int owner = thread_of(mb, type);
-        const long long gchunk = (long long) (mb_first - P.mb0) * 6 + c;
-        const bool fits = base + S.off[THREADS - 1] + S.len[THREADS - 1] <= P.out_cap;
-        if (!fits && tid == 0) atomicOr(P.err, 1u);
-        if (P.chunk_off != nullptr && mb < n_mb) P.chunk_off[gchunk] = (uint32_t) (base + O);
-        if (P.qcoef != nullptr && mb < n_mb) {
-            uint32_t* dst = reinterpret_cast<uint32_t*>(P.qcoef + gchunk * 64);
+    // optional per-chunk outputs (tests, decode side-info) need the coefficient buffer: before it is reused
+    if (P.qcoef != nullptr) {
+        const int c = tid, mb = c / 6, type = c - 6 * mb;
+        if (mb < n_mb) {
+            uint32_t* dst = reinterpret_cast<uint32_t*>(P.qcoef + ((long long) (mb_first - P.mb0) * 6 + c) * 64);
+            const int owner = thread_of(mb, type);
 #pragma unroll
             for (int i = 0; i < 16; i++) dst[i] = S.coef[coef_word(owner, i)];
         }
-        if (fits) {
+    }
+    __syncthreads();                                   // S.off complete; coefficient buffer free
+
+    // warp 0: decoupled look-back for the tile's payload offset
+    if (warp == 0) {
+        constexpr unsigned long long FLAG_AGG = 1ull << 62, FLAG_PFX = 2ull << 62, VMASK = (1ull << 62) - 1;
+        unsigned long long excl = 0;
+        if (tile > 0) {
+            if (lane == 0) st_desc(P.desc + tile, FLAG_AGG | total);
+            int base = tile - 1;
+            while (true) {
+                int idx = base - lane;
+                unsigned long long dsc = FLAG_PFX;                // virtual prefix 0 before tile 0
+                if (idx >= 0) { do { dsc = ld_desc(P.desc + idx); } while ((dsc >> 62) == 0); }
+                unsigned pm = __ballot_sync(0xffffffffu, (dsc >> 62) == 2);
+                int first = pm ? (__ffs((int) pm) - 1) : 31;
+                unsigned long long c = lane <= first ? (dsc & VMASK) : 0ull;
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+                excl += c;
+                if (pm) break;
+                base -= 32;
+            }
+        }
+        if (lane == 0) {
+            st_desc(P.desc + tile, FLAG_PFX | (excl + total));
+            S.tile_base = excl;
+            if (mb_first + n_mb >= P.mb1) *P.out_len = excl + total;      // last tile: payload length
+        }
+    }
+    // meanwhile / afterwards: every thread moves its own chunk to its place in the compacted tile
+    const bool compact_ok = total + 4 <= COMPACT_CAP;
+    uint8_t* compact = reinterpret_cast<uint8_t*>(S.coef);
+    if (compact_ok) {
+        const uint8_t* src = S.raw + tid * SLOT;
+        uint8_t* dst = compact + S.off[my_chunk];
+        for (uint32_t i = 0; i < my_len; i++) dst[i] = src[i];
+    }
+    __syncthreads();
+
+    // ---- F: the tile's bytes go to their final place
+    {
+        const unsigned long long base = S.tile_base;
+        const bool fits = base + total <= P.out_cap;
+        if (!fits && tid == 0) atomicOr(P.err, 1u);
+        if (P.chunk_off != nullptr) {
+            const int c = tid;
+            if (c < n_mb * 6) P.chunk_off[(long long) (mb_first - P.mb0) * 6 + c] = (uint32_t) (base + S.off[c]);
+        }
+        if (fits && compact_ok) {
+            uint8_t* out = P.out + base;
+            const uint32_t head = min(total, (uint32_t) ((4 - (reinterpret_cast<uintptr_t>(out) & 3)) & 3));
+            if (tid < head) out[tid] = compact[tid];
+            const uint32_t n_words = (total - head) >> 2;
+            const uint32_t* cw = reinterpret_cast<const uint32_t*>(compact);
+            uint32_t* ow = reinterpret_cast<uint32_t*>(out + head);
+            const uint32_t sh = head * 8;
+            for (uint32_t j = tid; j < n_words; j += THREADS) {
+                // bytes compact[head + 4j .. +4): two aligned words, funnel-shifted
+                uint32_t lo = cw[j], hi = cw[j + 1];
+                ow[j] = head ? __funnelshift_r(lo, hi, sh) : lo;
+            }
+            const uint32_t tail0 = head + (n_words << 2);
+            if (tail0 + tid < total) out[tail0 + tid] = compact[tail0 + tid];
+        } else if (fits) {                              // oversized tile (> 64 B per chunk on average): direct scatter
+            const int c = tid, mb = c / 6, type = c - 6 * mb;
+            const uint32_t L = S.len[c], O = S.off[c];
+            const int owner = thread_of(mb, type);
             for (int j = 0; j < 32; j++) {
                 uint32_t Lj = __shfl_sync(0xffffffffu, L, j);
                 uint32_t Oj = __shfl_sync(0xffffffffu, O, j);
@@ -390,6 +488,9 @@ cudaError_t launch_encode(const EncParams& P, int n_tiles, cudaStream_t stream) 
     if (dev < 64 && !attr_set[dev]) {
         cudaError_t e = cudaFuncSetAttribute(awi_encode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              (int) sizeof(EncSmem));
+        if (e != cudaSuccess) return e;
+        e = cudaFuncSetAttribute(awi_encode_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                 cudaSharedmemCarveoutMaxShared);
         if (e != cudaSuccess) return e;
         attr_set[dev] = true;
     }

@@ -252,7 +252,12 @@ int gpu_codec_device_count(void) {
 
 bool gpu_codec_init_devices(const int* ids, int n) {
     std::lock_guard<std::mutex> lk(g_mu);
-    if (!g_ctx.empty()) return fail("already initialised (call gpu_codec_shutdown first)");
+    if (!g_ctx.empty()) {                       // idempotent for the same device list
+        bool same = ids && n == (int) g_ctx.size();
+        for (int i = 0; same && i < n; i++) same = g_ctx[i]->dev == ids[i];
+        if (same) return true;
+        return fail("already initialised on a different device list (call gpu_codec_shutdown first)");
+    }
     int have = gpu_codec_device_count();
     if (have == 0) return fail("no CUDA device available; this library has no CPU path");
     if (n <= 0 || !ids) return fail("init: need at least one device");

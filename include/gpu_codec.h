@@ -50,7 +50,8 @@ int gpu_codec_device_count(void);
  * lazy cosine-table initialisation, dct.c:11-23, happens here instead). */
 bool gpu_codec_init(int n_gpus);
 
-/* Same, on an explicit device list (one process per GPU launches pass their own id). */
+/* Same, on an explicit device list (one process per GPU launches pass their own id).
+ * Calling init again with the list already in use is a no-op that returns true. */
 bool gpu_codec_init_devices(const int* device_ids, int n);
 
 void gpu_codec_shutdown(void);
