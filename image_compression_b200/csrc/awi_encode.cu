@@ -7,13 +7,17 @@
 //
 //   tile = 32 consecutive macroblocks (raster order), one CTA of 6 warps
 //   A  coalesced 128-bit loads of the tile's 16 pixel rows (bottom-up BGR) -> smem
-//   B  one thread per 8x8 block: colour -> AAN DCT -> quantise (+ambiguity flags)
-//      -> scan-order int8 coefficients in smem;  exact DC;  halo macroblock DCs
+//   B  8 lanes per 8x8 block (one image row each, then one column each): colour ->
+//      AAN row pass in registers -> 8x8 transpose through padded smem -> AAN column
+//      pass -> quantise (+ambiguity flags) with per-lane constants held in registers
+//      -> scan-order int8 coefficients in smem;  exact DC;  halo macroblock DCs.
+//      A warp walks 32 blocks in 8 iterations of a short loop (small instruction
+//      footprint, ~60 registers: 4-5 CTAs per SM).
 //   C  flagged coefficients recomputed warp-cooperatively in the reference's exact
 //      operation order
 //   D  one thread per chunk: run-length symbols + bit packing into a smem slot
 //   E  CTA scan of chunk byte lengths; warp 0 resolves the tile's payload offset by
-//      decoupled look-back while the other warps compact the slots in smem
+//      decoupled look-back (128 descriptors per round) while the others compact
 //   F  coalesced word copy of the compacted tile to its final payload offset
 //
 // Chunks are byte aligned (rle.c:107) so the device-wide scan is over BYTE lengths.
@@ -31,56 +35,48 @@ namespace awi {
 #define ENC_MIN_CTAS 4                           // resident CTAs per SM the register budget is sized for
 #endif
 constexpr int TILE_MB = ENC_TILE_MB;             // 32 macroblocks per tile
-constexpr int THREADS = 192;                     // one thread per 8x8 block of the tile
+constexpr int THREADS = 192;                     // = chunks per tile; phase B: 24 blocks-at-a-time of 8 lanes
 constexpr int NWARPS = THREADS / 32;
-constexpr int ROW_BYTES = TILE_MB * 48;          // one pixel row of the tile in smem
-constexpr int RAW_BYTES = 16 * ROW_BYTES;        // 24576
+constexpr int PITCH = TILE_MB * 48 + 16;         // smem bytes per pixel row: 388 words = 4 mod 32 -> the 8 rows of a
+                                                 // block land 4 banks apart, conflict-free 64-bit row reads
+constexpr int RAW_BYTES = 16 * PITCH;            // 24832
 constexpr int SLOT = 124;                        // staging bytes per chunk (max 121), 31 words: conflict-free
 constexpr int COMPACT_CAP = THREADS * 64;        // compacted tile lives in the (dead) coefficient buffer
+constexpr int TR_WORDS = 4 * 72;                 // per warp: 4 blocks x 8 rows x (8 + 1 pad) floats
 static_assert(THREADS * SLOT <= RAW_BYTES, "chunk slots alias the raw tile");
 static_assert(THREADS == 2 * TILE_MB * 3, "loader: one fixed (macroblock, 16-byte piece) per thread, two rows per pass");
+static_assert(THREADS == TILE_MB * 6, "one thread per chunk in phases D-F");
 
 struct __align__(16) EncSmem {
     uint8_t raw[RAW_BYTES];                      // phase A-C: pixels; phase D-F: chunk slots
     uint8_t halo[16 * 48];                       // macroblock preceding the tile
-    uint32_t coef[THREADS * 16];                 // int8[64] per block, scan order, quads swizzled; phase E-F: compacted tile
-    unsigned long long amb[THREADS];             // per block: natural positions to recompute
+    uint32_t coef[THREADS * 16];                 // int8[64] per chunk, scan order, quads swizzled; phase E-F: compacted tile
+    float tr[NWARPS][TR_WORDS];                  // phase B transposes
+    unsigned long long amb[THREADS];             // per chunk: natural positions to recompute
     float cosf[64];
     int dc[(TILE_MB + 1) * 6];                   // quantised DCs, [0] = halo macroblock
     int halo_sum[6];
     uint32_t len[THREADS];                       // chunk byte lengths, chunk order
     uint32_t off[THREADS];                       // exclusive offsets inside the tile
     uint32_t warp_tot[NWARPS];
-    uint16_t amb_list[THREADS];                  // threads whose block has flagged coefficients
+    uint16_t amb_list[THREADS];                  // chunks with flagged coefficients
     int amb_count;
     unsigned long long tile_base;
     int tile;
 };
 
-// thread -> block mapping.  Warps 0..3: luma, block row i = warp&1, macroblock half
-// hm = warp>>1, lane = 2*m' + j (so a warp reads 32 horizontally adjacent 8-pixel
-// groups: 24-byte lane stride, conflict-free 64-bit smem loads).  Warps 4,5: chroma,
-// hm = warp-4, lanes 0-15 Cb, 16-31 Cr of macroblock m' = lane&15.
-struct BlockId { int mb; int type; };            // type: 0..3 = Y[i][j], 4 = Cb, 5 = Cr
-__device__ __forceinline__ BlockId block_of(int tid) {
-    int w = tid >> 5, l = tid & 31;
-    BlockId b;
-    if (w < 4) { b.mb = ((w >> 1) << 4) + (l >> 1); b.type = ((w & 1) << 1) | (l & 1); }
-    else { b.mb = ((w - 4) << 4) + (l & 15); b.type = 4 + (l >> 4); }
-    return b;
+// chunk index inside the tile: 6*macroblock + type, type 0..3 = Y[i][j], 4 = Cb, 5 = Cr
+__device__ __forceinline__ int coef_word(int chunk, int word) {    // swizzled word index
+    return chunk * 16 + ((((word >> 2) ^ (chunk >> 1)) & 3) << 2) + (word & 3);
 }
-__device__ __forceinline__ int thread_of(int mb, int type) {
-    if (type < 4) return ((((mb >> 4) << 1) | (type >> 1)) << 5) + ((mb & 15) << 1) + (type & 1);
-    return ((4 + (mb >> 4)) << 5) + ((type - 4) << 4) + (mb & 15);
-}
-__device__ __forceinline__ int coef_word(int tid, int word) {      // swizzled word index
-    return tid * 16 + ((((word >> 2) ^ (tid >> 1)) & 3) << 2) + (word & 3);
+__device__ __forceinline__ int coef_byte(int chunk, int idx) {     // swizzled byte index of scan position idx
+    return chunk * 64 + ((((idx >> 4) ^ (chunk >> 1)) & 3) << 4) + (idx & 15);
 }
 
 // Look-back descriptors carry value and state in one 64-bit word, so relaxed accesses are
 // enough (no other data is published through them) — and unlike ld.acquire they do not
 // invalidate the SM's L1 on every poll.
-__device__ __forceinline__ uint64_t ld_desc(const unsigned long long* p) {
+__device__ __forceinline__ unsigned long long ld_desc(const unsigned long long* p) {
     unsigned long long v;
     asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
     return v;
@@ -115,8 +111,7 @@ __device__ __forceinline__ uint4 load_piece(const uint8_t* src, int valid, int a
 __device__ __forceinline__ int byte_of(uint32_t w, int i) { return (int) ((w >> (8 * i)) & 0xffu); }
 
 // The literal fp64 expressions (color.c:31-33) are needed for roughly one pixel in a
-// thousand.  Kept out of line: one copy each instead of one per unrolled pixel, which is
-// what keeps the hot loop's instruction footprint small.
+// thousand.  Kept out of line so the hot loop stays small.
 __device__ __noinline__ int luma_exact_call(int r, int g, int b) { return y_exact(r, g, b); }
 __device__ __noinline__ int chroma_exact_call(int r, int g, int b, int cr) { return cr ? cr_exact(r, g, b) : cb_exact(r, g, b); }
 
@@ -181,16 +176,16 @@ __device__ __forceinline__ void chroma_row(const uint32_t* w, float* d, int kr, 
     }
 }
 
-// sample (row y, column x) of the block owned by thread `tid`, recomputed from raw pixels
-__device__ __forceinline__ int sample_of(const EncSmem& S, int tid, int y, int x) {
-    BlockId id = block_of(tid);
+// sample (row y, column x) of chunk `chunk` of the tile, recomputed from the raw pixels
+__device__ __forceinline__ int sample_of(const EncSmem& S, int chunk, int y, int x) {
+    const int mb = chunk / 6, type = chunk - 6 * mb;
     int row, col;
-    if (id.type < 4) { row = ((id.type >> 1) << 3) + y; col = id.mb * 48 + ((id.type & 1) * 8 + x) * 3; }
-    else { row = 2 * y; col = id.mb * 48 + 6 * x; }
-    const uint8_t* p = S.raw + row * ROW_BYTES + col;
+    if (type < 4) { row = ((type >> 1) << 3) + y; col = mb * 48 + ((type & 1) * 8 + x) * 3; }
+    else { row = 2 * y; col = mb * 48 + 6 * x; }
+    const uint8_t* p = S.raw + row * PITCH + col;
     int b = p[0], g = p[1], r = p[2];
-    if (id.type < 4) return luma_of(r, g, b);
-    return chroma_of(r, g, b, id.type == 5);
+    if (type < 4) return luma_of(r, g, b);
+    return chroma_of(r, g, b, type == 5);
 }
 
 // ---------------------------------------------------------------- the kernel
@@ -203,6 +198,7 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
     if (tid == 0) { S.tile = (int) atomicAdd(P.ticket, 1u); S.amb_count = 0; }
     if (tid < 64) S.cosf[tid] = __uint_as_float(cos_bits_rt(tid));
     if (tid < 6) S.halo_sum[tid] = 0;
+    S.amb[tid] = 0;
     __syncthreads();
     const int tile = S.tile;
     const int mb_first = P.mb0 + tile * TILE_MB;                 // global raster index
@@ -227,9 +223,9 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
             for (int i = 0; i < 8; i++)
                 if (y0 + 2 * i < P.height) v[i] = load_piece(src - (long long) (2 * i) * P.stride, valid, P.align);
         }
-        uint4* dst = reinterpret_cast<uint4*>(S.raw) + r0 * (3 * TILE_MB) + col;
+        uint8_t* dst = S.raw + r0 * PITCH + col * 16;
 #pragma unroll
-        for (int i = 0; i < 8; i++) dst[i * 2 * (3 * TILE_MB)] = v[i];
+        for (int i = 0; i < 8; i++) *reinterpret_cast<uint4*>(dst + i * 2 * PITCH) = v[i];
         if (tid < 48) {
             uint4 h = make_uint4(0, 0, 0, 0);
             if (has_halo) {
@@ -244,45 +240,92 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
     }
     __syncthreads();
 
-    // ---- B: colour + DCT + quantise, one block per thread
-    const BlockId me = block_of(tid);
-    const bool active = me.mb < n_mb;
-    uint64_t amb = 0;
-    if (active) {
-        float d[64];
-        uint32_t packed[16];
-        if (warp < 4) {
-            const uint8_t* base = S.raw + ((me.type >> 1) << 3) * ROW_BYTES + me.mb * 48 + (me.type & 1) * 24;
+    // ---- B: colour + DCT + quantise; 8 lanes per block, 4 blocks per warp per iteration
+    {
+        const int v = lane & 7, jb = lane >> 3;                   // v: my row in pass 1, my column in pass 2
+        const bool chroma = warp >= 4;
+        // per-lane quantiser constants for natural positions (u, v), u = 0..7, and where
+        // their quantised values go in the chunk
+        float gk[8], gc[8], gt[8];
+        uint32_t pos_lo = 0, pos_hi = 0;                          // 8 x 8-bit scan positions
 #pragma unroll
-            for (int y = 0; y < 8; y++) {
-                const uint2* src = reinterpret_cast<const uint2*>(base + y * ROW_BYTES);
-                uint2 a = src[0], b = src[1], c = src[2];
-                uint32_t w[6] = { a.x, a.y, b.x, b.y, c.x, c.y };
-                luma_row(w, d + 8 * y);
-            }
-            fdct_quant_pack<false>(d, packed, amb);
-        } else {
-            const uint8_t* base = S.raw + me.mb * 48;
-            const int cr = me.type == 5;
-            const int kr = cr ? 5000 : -1687, kg = cr ? -4187 : -3313, kb = cr ? -813 : 5000;
-#pragma unroll
-            for (int y = 0; y < 8; y++) {
-                const uint4* src = reinterpret_cast<const uint4*>(base + 2 * y * ROW_BYTES);
-                uint4 a = src[0], b = src[1], c = src[2];
-                uint32_t w[12] = { a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w, c.x, c.y, c.z, c.w };
-                chroma_row(w, d + 8 * y, kr, kg, kb, cr);
-            }
-            fdct_quant_pack<true>(d, packed, amb);
+        for (int u = 0; u < 8; u++) {
+            gk[u] = d_gk[chroma][8 * u + v];
+            gc[u] = d_gc[chroma][8 * u + v];
+            gt[u] = d_gt[chroma][8 * u + v];
+            uint32_t p = (uint32_t) unscan_rt(8 * u + v);
+            if (u < 4) pos_lo |= p << (8 * u); else pos_hi |= p << (8 * (u - 4));
         }
+        float* tr = S.tr[warp];
+        uint8_t* coefb = reinterpret_cast<uint8_t*>(S.coef);
+        const int kr = jb & 1 ? 5000 : -1687, kg = jb & 1 ? -4187 : -3313, kb = jb & 1 ? -813 : 5000;
+
+        for (int it = 0; it < 8; it++) {
+            int mb, type;
+            if (!chroma) {            // warp = 2*half + block-row; 32 horizontally adjacent blocks per warp
+                const int c = ((warp >> 1) << 5) + 4 * it + jb;
+                mb = c >> 1;
+                type = ((warp & 1) << 1) | (c & 1);
+            } else {                  // 16 macroblocks per warp, (Cb, Cr) pairs
+                mb = ((warp - 4) << 4) + 2 * it + (jb >> 1);
+                type = 4 + (jb & 1);
+            }
+            const int chunk = mb * 6 + type;
+            const bool active = mb < n_mb;
+            float d[8];
+            if (!chroma) {
+                const uint8_t* src = S.raw + (((type >> 1) << 3) + v) * PITCH + mb * 48 + (type & 1) * 24;
+                const uint2* s2 = reinterpret_cast<const uint2*>(src);
+                uint2 a = s2[0], b = s2[1], c2 = s2[2];
+                uint32_t w[6] = { a.x, a.y, b.x, b.y, c2.x, c2.y };
+                luma_row(w, d);
+            } else {
+                const uint4* s4 = reinterpret_cast<const uint4*>(S.raw + 2 * v * PITCH + mb * 48);
+                uint4 a = s4[0], b = s4[1], c4 = s4[2];
+                uint32_t w[12] = { a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w, c4.x, c4.y, c4.z, c4.w };
+                chroma_row(w, d, kr, kg, kb, jb & 1);
+            }
+            aan8(d[0], d[1], d[2], d[3], d[4], d[5], d[6], d[7]);                 // row pass
+            __syncwarp();
 #pragma unroll
-        for (int q4 = 0; q4 < 4; q4++) {
-            uint4 v = make_uint4(packed[4 * q4], packed[4 * q4 + 1], packed[4 * q4 + 2], packed[4 * q4 + 3]);
-            *reinterpret_cast<uint4*>(&S.coef[coef_word(tid, 4 * q4)]) = v;
-        }
-        S.dc[(me.mb + 1) * 6 + me.type] = (int) (int8_t) (packed[0] & 0xff);
-        if (amb != 0) {
-            S.amb[tid] = amb;
-            S.amb_list[atomicAdd(&S.amb_count, 1)] = (uint16_t) tid;
+            for (int x = 0; x < 8; x++) tr[jb * 72 + v * 9 + x] = d[x];
+            __syncwarp();
+#pragma unroll
+            for (int u = 0; u < 8; u++) d[u] = tr[jb * 72 + u * 9 + v];
+            aan8(d[0], d[1], d[2], d[3], d[4], d[5], d[6], d[7]);                 // column pass: d[u] = coefficient (u, v)
+
+            uint32_t flags = 0;
+            float t[8];
+#pragma unroll
+            for (int u = 0; u < 8; u++) flags |= quant_flag(d[u], gk[u], gc[u], gt[u], t[u]) ? (1u << u) : 0u;
+            uint32_t q0 = __float_as_uint(t[0]);
+            if (v == 0) {             // exact DC: d[0] is the integer sum of the 64 centred samples
+                const int q = quant_int(dc_coef_from_sum((int) d[0]), chroma ? 17 : 16);
+                q0 = (uint32_t) q;
+                flags &= ~1u;
+                if (active) S.dc[(mb + 1) * 6 + type] = q;
+            }
+            if (active) {
+                coefb[coef_byte(chunk, pos_lo & 0xff)] = (uint8_t) q0;
+#pragma unroll
+                for (int u = 1; u < 8; u++) {
+                    const uint32_t p = ((u < 4 ? pos_lo : pos_hi) >> (8 * (u & 3))) & 0xff;
+                    coefb[coef_byte(chunk, p)] = (uint8_t) __float_as_uint(t[u]);
+                }
+            } else {
+                flags = 0;
+            }
+            const unsigned any = __ballot_sync(0xffffffffu, flags != 0);
+            if (any) {                // rare: remember which coefficients to redo exactly
+                if (flags) {
+                    unsigned long long m = 0;
+#pragma unroll
+                    for (int u = 0; u < 8; u++) if (flags & (1u << u)) m |= 1ull << (8 * u + v);
+                    atomicOr(&S.amb[chunk], m);
+                }
+                const unsigned grp = (any >> (8 * jb)) & 0xffu;
+                if (grp && v == __ffs((int) grp) - 1) S.amb_list[atomicAdd(&S.amb_count, 1)] = (uint16_t) chunk;
+            }
         }
     }
 
@@ -319,7 +362,7 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
     for (int e = warp; e < n_amb; e += NWARPS) {
         const int b = S.amb_list[e];
         unsigned long long m = S.amb[b];
-        const bool chroma = b >= 128;
+        const bool chroma = (b % 6) >= 4;
         while (m) {
             int k = __ffsll((long long) m) - 1;
             m &= m - 1;
@@ -333,16 +376,16 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
             if (lane == 0) {
                 int c = exact_coef_finish(part, u, v);
                 int q = quant_int(c, chroma ? qchroma_rt(k) : qluma_rt(k));
-                int idx = unscan_rt(k);
-                reinterpret_cast<int8_t*>(&S.coef[coef_word(b, idx >> 2)])[idx & 3] = (int8_t) q;
+                reinterpret_cast<int8_t*>(S.coef)[coef_byte(b, unscan_rt(k))] = (int8_t) q;
             }
         }
     }
     __syncthreads();                                   // raw pixels are dead from here on
 
-    // ---- D: run-length + bit packing, one chunk per thread, into its slot
+    // ---- D: run-length + bit packing, thread = chunk, into its slot
     uint32_t my_len = 0;
-    if (active) {
+    const int my_mb = tid / 6, my_type = tid - 6 * my_mb;
+    if (my_mb < n_mb) {
         uint32_t w[16];
 #pragma unroll
         for (int q4 = 0; q4 < 4; q4++) {
@@ -357,51 +400,43 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
             uint32_t nib = ((nz >> 7) * 0x10204080u) >> 28;
             if (i < 8) lo |= nib << (4 * i); else hi |= nib << (4 * (i - 8));
         }
-        const uint8_t* cbase = reinterpret_cast<const uint8_t*>(S.coef);
-        const int swz = (tid >> 1) & 3;
-        auto coef = [&](int i) -> int {
-            return (int) (int8_t) cbase[tid * 64 + ((((i >> 4) ^ swz) & 3) << 4) + (i & 15)];
-        };
+        const int8_t* cbase = reinterpret_cast<const int8_t*>(S.coef);
+        auto coef = [&](int i) -> int { return (int) cbase[coef_byte(tid, i)]; };
         uint32_t* slot = reinterpret_cast<uint32_t*>(S.raw + tid * SLOT);
         auto put = [&](int word, uint32_t be) { slot[word] = __byte_perm(be, 0, 0x0123); };
-        int dc = S.dc[(me.mb + 1) * 6 + me.type];
-        int prev = S.dc[me.mb * 6 + me.type];
+        int dc = S.dc[(my_mb + 1) * 6 + my_type];
+        int prev = S.dc[my_mb * 6 + my_type];
         my_len = (uint32_t) rle_chunk(dc, prev, ((unsigned long long) hi << 32) | lo, coef, put);
     }
-    const int my_chunk = me.mb * 6 + me.type;
-    S.len[my_chunk] = my_len;
-    __syncthreads();
 
-    // ---- E: offsets inside the tile (chunk order = tid order here)
-    uint32_t total;
+    // ---- E: offsets inside the tile
+    uint32_t total, my_off;
     {
-        uint32_t v = S.len[tid], incl = v;
+        uint32_t incl = my_len;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
             uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
             if (lane >= o) incl += t;
         }
         if (lane == 31) S.warp_tot[warp] = incl;
-        __syncthreads();
+        __syncthreads();                                // also: every slot written, coefficients no longer read by D
         uint32_t wbase = 0;
         total = 0;
 #pragma unroll
         for (int i = 0; i < NWARPS; i++) { uint32_t t = S.warp_tot[i]; if (i < warp) wbase += t; total += t; }
-        S.off[tid] = wbase + incl - v;
+        my_off = wbase + incl - my_len;
     }
     // optional per-chunk outputs (tests, decode side-info) need the coefficient buffer: before it is reused
     if (P.qcoef != nullptr) {
-        const int c = tid, mb = c / 6, type = c - 6 * mb;
-        if (mb < n_mb) {
-            uint32_t* dst = reinterpret_cast<uint32_t*>(P.qcoef + ((long long) (mb_first - P.mb0) * 6 + c) * 64);
-            const int owner = thread_of(mb, type);
+        if (my_mb < n_mb) {
+            uint32_t* dst = reinterpret_cast<uint32_t*>(P.qcoef + ((long long) (mb_first - P.mb0) * 6 + tid) * 64);
 #pragma unroll
-            for (int i = 0; i < 16; i++) dst[i] = S.coef[coef_word(owner, i)];
+            for (int i = 0; i < 16; i++) dst[i] = S.coef[coef_word(tid, i)];
         }
+        __syncthreads();
     }
-    __syncthreads();                                   // S.off complete; coefficient buffer free
 
-    // warp 0: decoupled look-back for the tile's payload offset
+    // warp 0: decoupled look-back for the tile's payload offset, 4 descriptors per lane per round
     if (warp == 0) {
         constexpr unsigned long long FLAG_AGG = 1ull << 62, FLAG_PFX = 2ull << 62, VMASK = (1ull << 62) - 1;
         unsigned long long excl = 0;
@@ -409,17 +444,32 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
             if (lane == 0) st_desc(P.desc + tile, FLAG_AGG | total);
             int base = tile - 1;
             while (true) {
-                int idx = base - lane;
-                unsigned long long dsc = FLAG_PFX;                // virtual prefix 0 before tile 0
-                if (idx >= 0) { do { dsc = ld_desc(P.desc + idx); } while ((dsc >> 62) == 0); }
-                unsigned pm = __ballot_sync(0xffffffffu, (dsc >> 62) == 2);
-                int first = pm ? (__ffs((int) pm) - 1) : 31;
-                unsigned long long c = lane <= first ? (dsc & VMASK) : 0ull;
+                unsigned long long dsc[4];
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    const int idx = base - 4 * lane - j;
+                    dsc[j] = idx >= 0 ? ld_desc(P.desc + idx) : FLAG_PFX;      // virtual prefix 0 before tile 0
+                }
+                // only descriptors up to the nearest prefix matter; wait for those
+                unsigned long long sum = 0;
+                bool found = false;
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    if (!found) {
+                        const int idx = base - 4 * lane - j;
+                        while ((dsc[j] >> 62) == 0) { __nanosleep(40); dsc[j] = ld_desc(P.desc + idx); }
+                        sum += dsc[j] & VMASK;
+                        found = (dsc[j] >> 62) == 2;
+                    }
+                }
+                const unsigned pm = __ballot_sync(0xffffffffu, found);
+                const int first = pm ? (__ffs((int) pm) - 1) : 31;
+                unsigned long long c = lane <= first ? sum : 0ull;
 #pragma unroll
                 for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
                 excl += c;
                 if (pm) break;
-                base -= 32;
+                base -= 128;
             }
         }
         if (lane == 0) {
@@ -433,8 +483,11 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
     uint8_t* compact = reinterpret_cast<uint8_t*>(S.coef);
     if (compact_ok) {
         const uint8_t* src = S.raw + tid * SLOT;
-        uint8_t* dst = compact + S.off[my_chunk];
+        uint8_t* dst = compact + my_off;
         for (uint32_t i = 0; i < my_len; i++) dst[i] = src[i];
+    } else {
+        S.len[tid] = my_len;
+        S.off[tid] = my_off;
     }
     __syncthreads();
 
@@ -443,10 +496,8 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
         const unsigned long long base = S.tile_base;
         const bool fits = base + total <= P.out_cap;
         if (!fits && tid == 0) atomicOr(P.err, 1u);
-        if (P.chunk_off != nullptr) {
-            const int c = tid;
-            if (c < n_mb * 6) P.chunk_off[(long long) (mb_first - P.mb0) * 6 + c] = (uint32_t) (base + S.off[c]);
-        }
+        if (P.chunk_off != nullptr && my_mb < n_mb)
+            P.chunk_off[(long long) (mb_first - P.mb0) * 6 + tid] = (uint32_t) (base + my_off);
         if (fits && compact_ok) {
             uint8_t* out = P.out + base;
             const uint32_t head = min(total, (uint32_t) ((4 - (reinterpret_cast<uintptr_t>(out) & 3)) & 3));
@@ -458,19 +509,15 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
             for (uint32_t j = tid; j < n_words; j += THREADS) {
                 // bytes compact[head + 4j .. +4): two aligned words, funnel-shifted
                 uint32_t lo = cw[j], hi = cw[j + 1];
-                ow[j] = head ? __funnelshift_r(lo, hi, sh) : lo;
+                ow[j] = __funnelshift_r(lo, hi, sh);
             }
             const uint32_t tail0 = head + (n_words << 2);
             if (tail0 + tid < total) out[tail0 + tid] = compact[tail0 + tid];
         } else if (fits) {                              // oversized tile (> 64 B per chunk on average): direct scatter
-            const int c = tid, mb = c / 6, type = c - 6 * mb;
-            const uint32_t L = S.len[c], O = S.off[c];
-            const int owner = thread_of(mb, type);
             for (int j = 0; j < 32; j++) {
-                uint32_t Lj = __shfl_sync(0xffffffffu, L, j);
-                uint32_t Oj = __shfl_sync(0xffffffffu, O, j);
-                int ownj = __shfl_sync(0xffffffffu, owner, j);
-                const uint8_t* src = S.raw + ownj * SLOT;
+                const int c = (warp << 5) + j;
+                const uint32_t Lj = S.len[c], Oj = S.off[c];
+                const uint8_t* src = S.raw + c * SLOT;
                 uint8_t* dst = P.out + base + Oj;
                 for (uint32_t i = lane; i < Lj; i += 32) dst[i] = src[i];
             }

@@ -17,6 +17,10 @@ static __device__ const int d_qchroma[64] = AWI_QCHROMA;
 static __device__ const int d_unscan[64] = AWI_UNSCAN;
 static __device__ const int d_scan[64] = AWI_SCAN;
 static __device__ const uint32_t d_cos_bits[64] = AWI_COS_BITS;
+// fast-path quantiser constants, [0] luma, [1] chroma (codec_math.cuh quant_flag)
+static __device__ const float d_gk[2][64] = { AWI_GK_LUMA, AWI_GK_CHROMA };
+static __device__ const float d_gc[2][64] = { AWI_GC_LUMA, AWI_GC_CHROMA };
+static __device__ const float d_gt[2][64] = { AWI_GT_LUMA, AWI_GT_CHROMA };
 __device__ __forceinline__ int qluma_rt(int k) { return d_qluma[k]; }
 __device__ __forceinline__ int qchroma_rt(int k) { return d_qchroma[k]; }
 __device__ __forceinline__ int unscan_rt(int k) { return d_unscan[k]; }

@@ -222,6 +222,21 @@ AWI_HD int quant_int(int c, int Q) {
     return c < 0 ? -q : q;
 }
 
+// Quantise one AAN-scaled coefficient x at a position with constants (gk, gc, gt) from
+// codec_tables.h:  g = x*gk - sign(x)*gc,  q = rn(g).  Returns q as the float q + 1.5*2^23,
+// whose low mantissa byte is q in two's complement, and whether the result is ambiguous
+// (|g - q| > gt), i.e. the reference could have rounded the other way.  gc = 0 for even
+// quantiser steps: fma(x, gk, -+0) is then the plain rounded product.
+AWI_HD bool quant_flag(float x, float gk, float gc, float gt, float& t) {
+    const float MAGIC = 12582912.0f;   // 1.5 * 2^23
+    float sc = u2f(f2u(gc) | ((f2u(x) & 0x80000000u) ^ 0x80000000u));   // -sign(x)*gc
+    float g = fma_rn(x, gk, sc);
+    t = g + MAGIC;
+    float n = t - MAGIC;
+    float diff = g - n;
+    return (diff < 0 ? -diff : diff) > gt;
+}
+
 // Fast DCT + quantise + scan-order pack of one 8x8 block held in registers.
 //   d[64]  in: centred samples, natural [y][x] order (destroyed)
 //   packed out: 64 int8 quantised coefficients in chunk (scan) order, 4 per word, LE
@@ -237,24 +252,13 @@ AWI_HD void fdct_quant_pack(float* d, uint32_t* packed, uint64_t& amb) {
         aan8(d[x], d[8 + x], d[16 + x], d[24 + x], d[32 + x], d[40 + x], d[48 + x], d[56 + x]);
 
     uint32_t lo = 0, hi = 0;
-    const float MAGIC = 12582912.0f;   // 1.5 * 2^23: low mantissa bits of (g + MAGIC) are rn(g) in two's complement
 #pragma unroll
     for (int k = 1; k < 64; k++) {
         const float gk = CHROMA ? gk_chroma(k) : gk_luma(k);
         const float gc = CHROMA ? gc_chroma(k) : gc_luma(k);
         const float gt = CHROMA ? gt_chroma(k) : gt_luma(k);
-        float x = d[k];
-        float g;
-        if (gc != 0.0f) {
-            float sc = u2f(f2u(gc) | ((f2u(x) & 0x80000000u) ^ 0x80000000u));   // -sign(x)*gc
-            g = fma_rn(x, gk, sc);
-        } else {
-            g = x * gk;
-        }
-        float t = g + MAGIC;
-        float n = t - MAGIC;
-        float diff = g - n;
-        bool a = (diff < 0 ? -diff : diff) > gt;
+        float t;
+        bool a = quant_flag(d[k], gk, gc, gt, t);
         if (k < 32) lo |= a ? (1u << k) : 0u; else hi |= a ? (1u << (k - 32)) : 0u;
         d[k] = t;
     }
