@@ -50,7 +50,7 @@ static_assert(THREADS == TILE_MB * 6, "one thread per chunk in phases D-F");
 struct __align__(16) EncSmem {
     uint8_t raw[RAW_BYTES];                      // phase A-C: pixels; phase D-F: chunk slots
     uint8_t halo[16 * 48];                       // macroblock preceding the tile
-    uint32_t coef[THREADS * 16];                 // int8[64] per chunk, scan order, quads swizzled; phase E-F: compacted tile
+    uint32_t coef[THREADS * 16];                 // int8[64] per chunk, scan order; phase E-F: compacted tile
     float tr[NWARPS][TR_WORDS];                  // phase B transposes
     unsigned long long amb[THREADS];             // per chunk: natural positions to recompute
     float cosf[64];
@@ -66,12 +66,8 @@ struct __align__(16) EncSmem {
 };
 
 // chunk index inside the tile: 6*macroblock + type, type 0..3 = Y[i][j], 4 = Cb, 5 = Cr
-__device__ __forceinline__ int coef_word(int chunk, int word) {    // swizzled word index
-    return chunk * 16 + ((((word >> 2) ^ (chunk >> 1)) & 3) << 2) + (word & 3);
-}
-__device__ __forceinline__ int coef_byte(int chunk, int idx) {     // swizzled byte index of scan position idx
-    return chunk * 64 + ((((idx >> 4) ^ (chunk >> 1)) & 3) << 4) + (idx & 15);
-}
+__device__ __forceinline__ int coef_word(int chunk, int word) { return chunk * 16 + word; }
+__device__ __forceinline__ int coef_byte(int chunk, int idx) { return chunk * 64 + idx; }
 
 // Look-back descriptors carry value and state in one 64-bit word, so relaxed accesses are
 // enough (no other data is published through them) — and unlike ld.acquire they do not
@@ -115,23 +111,65 @@ __device__ __forceinline__ int byte_of(uint32_t w, int i) { return (int) ((w >> 
 __device__ __noinline__ int luma_exact_call(int r, int g, int b) { return y_exact(r, g, b); }
 __device__ __noinline__ int chroma_exact_call(int r, int g, int b, int cr) { return cr ? cr_exact(r, g, b) : cb_exact(r, g, b); }
 
+// dp2a: c + a.lo16 * b.byte[sel] + a.hi16 * b.byte[sel+1], sel = 0 (lo) or 2 (hi); the pixel bytes
+// are consumed straight from the packed words, no byte extraction.
+__device__ __forceinline__ uint32_t dp2a_lo_u(uint32_t a, uint32_t b, uint32_t c) {
+    uint32_t d; asm("dp2a.lo.u32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c)); return d;
+}
+__device__ __forceinline__ uint32_t dp2a_hi_u(uint32_t a, uint32_t b, uint32_t c) {
+    uint32_t d; asm("dp2a.hi.u32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c)); return d;
+}
+__device__ __forceinline__ int dp2a_lo_s(int a, uint32_t b, int c) {      // signed 16-bit coefficients, unsigned bytes
+    int d; asm("dp2a.lo.s32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c)); return d;
+}
+__device__ __forceinline__ int dp2a_hi_s(int a, uint32_t b, int c) {
+    int d; asm("dp2a.hi.s32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c)); return d;
+}
+__device__ __forceinline__ int pack16(int lo, int hi) { return (lo & 0xffff) | (hi << 16); }
+
+// luma numerator 299 r + 587 g + 114 b of the pixel whose B byte is byte `s` (0..3) of w[i]
+template <int S>
+__device__ __forceinline__ uint32_t luma_num(uint32_t wa, uint32_t wb) {
+    constexpr uint32_t BG = 114u | (587u << 16), R0 = 299u, ZB = 114u << 16, GR = 587u | (299u << 16);
+    if (S == 0) return dp2a_hi_u(R0, wa, dp2a_lo_u(BG, wa, 0u));
+    if (S == 1) return dp2a_hi_u(GR, wa, dp2a_lo_u(ZB, wa, 0u));
+    if (S == 2) return dp2a_lo_u(R0, wb, dp2a_hi_u(BG, wa, 0u));
+    return dp2a_lo_u(GR, wb, dp2a_hi_u(ZB, wa, 0u));
+}
+
+// n / 1000 and "n is an exact multiple of 1000" from one 32x32->64 multiply:
+// n * 4294968 = 2^32 * (n/1000) + 0.704 n, so the low word is below 179521 exactly for multiples
+// and above 4294967 otherwise (n <= 255000).
+__device__ __forceinline__ uint32_t div1000(uint32_t n, bool& multiple) {
+    unsigned long long p = (unsigned long long) n * 4294968ull;
+    multiple = (uint32_t) p < 2000000u;
+    return (uint32_t) (p >> 32);
+}
+// n / 10000 likewise: n * 3435974 = 2^35 * (n/10000) + 0.1632 n (n <= 2560000); bits 3..34 of the
+// product are below 52225 exactly for multiples and above 429495 otherwise.
+__device__ __forceinline__ uint32_t div10000(uint32_t n, bool& multiple) {
+    unsigned long long p = (unsigned long long) n * 3435974ull;
+    uint32_t hi = (uint32_t) (p >> 32), lo = (uint32_t) p;
+    multiple = __funnelshift_l(lo, hi, 29) < 200000u;
+    return hi >> 3;
+}
+
 // 8 pixels (24 bytes B,G,R,...) in 6 words -> 8 centred luma samples
 __device__ __forceinline__ void luma_row(const uint32_t* w, float* d) {
-    uint32_t zero_rem = 0;
+    uint32_t n[8];
+    n[0] = luma_num<0>(w[0], w[0]); n[1] = luma_num<3>(w[0], w[1]); n[2] = luma_num<2>(w[1], w[2]); n[3] = luma_num<1>(w[2], w[2]);
+    n[4] = luma_num<0>(w[3], w[3]); n[5] = luma_num<3>(w[3], w[4]); n[6] = luma_num<2>(w[4], w[5]); n[7] = luma_num<1>(w[5], w[5]);
+    bool any = false;
 #pragma unroll
     for (int x = 0; x < 8; x++) {
-        int b = byte_of(w[(3 * x) >> 2], (3 * x) & 3);
-        int g = byte_of(w[(3 * x + 1) >> 2], (3 * x + 1) & 3);
-        int r = byte_of(w[(3 * x + 2) >> 2], (3 * x + 2) & 3);
-        uint32_t n = (uint32_t) (299 * r + 587 * g + 114 * b);
-        uint32_t q = __umulhi(n, 4294968u);
-        zero_rem |= (n - q * 1000u == 0u) ? (1u << x) : 0u;
-        d[x] = centred((int) q);
+        bool mult;
+        d[x] = centred((int) div1000(n[x], mult));
+        any |= mult;
     }
-    if (zero_rem) {                                  // exact multiple of 1000 somewhere in the row: rare
+    if (any) {                                       // exact multiple of 1000 somewhere in the row: rare
 #pragma unroll
         for (int x = 0; x < 8; x++) {
-            if (zero_rem & (1u << x)) {
+            if (n[x] % 1000u == 0u) {
                 int b = byte_of(w[(3 * x) >> 2], (3 * x) & 3);
                 int g = byte_of(w[(3 * x + 1) >> 2], (3 * x + 1) & 3);
                 int r = byte_of(w[(3 * x + 2) >> 2], (3 * x + 2) & 3);
@@ -150,23 +188,30 @@ __device__ __forceinline__ int chroma_of(int r, int g, int b, bool cr) {
     return (int) q;
 }
 
-// 16 pixels (48 bytes) in 12 words -> samples of the 8 even pixels (color.c:82-83)
-__device__ __forceinline__ void chroma_row(const uint32_t* w, float* d, int kr, int kg, int kb, int cr) {
-    uint32_t zero_rem = 0;
+// 16 pixels (48 bytes) in 12 words -> samples of the 8 even pixels (color.c:82-83).
+// cBG = kb | kg<<16, cR = kr: signed 16-bit coefficient pairs of the Cb or Cr row.
+__device__ __forceinline__ void chroma_row(const uint32_t* w, float* d, int cBG, int cR, int cr) {
+    uint32_t n[8];
+#pragma unroll
+    for (int x = 0; x < 8; x += 2) {
+        // even pixel 2x starts at byte 0 of w[3x/2*... ]: pixels 0,2,4,6 start at byte 0 of words 0,3,6,9;
+        // pixels 1,3,5,7 start at byte 2 of words 1,4,7,10
+        const int wa = (6 * x) >> 2;               // x even: 6x is a multiple of 4... (x = 0,2,4,6 -> words 0,3,6,9)
+        n[x] = (uint32_t) dp2a_hi_s(cR, w[wa], dp2a_lo_s(cBG, w[wa], 1280000));
+        const int wb = (6 * (x + 1)) >> 2;         // words 1,4,7,10, byte offset 2
+        n[x + 1] = (uint32_t) dp2a_lo_s(cR, w[wb + 1], dp2a_hi_s(cBG, w[wb], 1280000));
+    }
+    bool any = false;
 #pragma unroll
     for (int x = 0; x < 8; x++) {
-        int b = byte_of(w[(6 * x) >> 2], (6 * x) & 3);
-        int g = byte_of(w[(6 * x + 1) >> 2], (6 * x + 1) & 3);
-        int r = byte_of(w[(6 * x + 2) >> 2], (6 * x + 2) & 3);
-        uint32_t n = (uint32_t) (kr * r + kg * g + kb * b + 1280000);
-        uint32_t q = __umulhi(n, 3435974u) >> 3;
-        zero_rem |= (n - q * 10000u == 0u) ? (1u << x) : 0u;
-        d[x] = centred((int) q);
+        bool mult;
+        d[x] = centred((int) div10000(n[x], mult));
+        any |= mult;
     }
-    if (zero_rem) {
+    if (any) {
 #pragma unroll
         for (int x = 0; x < 8; x++) {
-            if (zero_rem & (1u << x)) {
+            if (n[x] % 10000u == 0u) {
                 int b = byte_of(w[(6 * x) >> 2], (6 * x) & 3);
                 int g = byte_of(w[(6 * x + 1) >> 2], (6 * x + 1) & 3);
                 int r = byte_of(w[(6 * x + 2) >> 2], (6 * x + 2) & 3);
@@ -219,9 +264,14 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
             const int valid = P.width * 3 - xb;
             const int y0 = my * 16 + r0;
             const uint8_t* src = P.rows + (long long) (P.height - 1 - y0) * P.stride + xb;
+            if (P.align == 16 && valid >= 16 && y0 + 14 < P.height) {     // the common case: 8 plain 128-bit loads
 #pragma unroll
-            for (int i = 0; i < 8; i++)
-                if (y0 + 2 * i < P.height) v[i] = load_piece(src - (long long) (2 * i) * P.stride, valid, P.align);
+                for (int i = 0; i < 8; i++) v[i] = __ldg(reinterpret_cast<const uint4*>(src - (long long) (2 * i) * P.stride));
+            } else {
+#pragma unroll 1
+                for (int i = 0; i < 8; i++)
+                    if (y0 + 2 * i < P.height) v[i] = load_piece(src - (long long) (2 * i) * P.stride, valid, P.align);
+            }
         }
         uint8_t* dst = S.raw + r0 * PITCH + col * 16;
 #pragma unroll
@@ -247,18 +297,17 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
         // per-lane quantiser constants for natural positions (u, v), u = 0..7, and where
         // their quantised values go in the chunk
         float gk[8], gc[8], gt[8];
-        uint32_t pos_lo = 0, pos_hi = 0;                          // 8 x 8-bit scan positions
+        int pos[8];                                               // scan positions of my 8 coefficients
 #pragma unroll
         for (int u = 0; u < 8; u++) {
             gk[u] = d_gk[chroma][8 * u + v];
             gc[u] = d_gc[chroma][8 * u + v];
             gt[u] = d_gt[chroma][8 * u + v];
-            uint32_t p = (uint32_t) unscan_rt(8 * u + v);
-            if (u < 4) pos_lo |= p << (8 * u); else pos_hi |= p << (8 * (u - 4));
+            pos[u] = unscan_rt(8 * u + v);
         }
         float* tr = S.tr[warp];
         uint8_t* coefb = reinterpret_cast<uint8_t*>(S.coef);
-        const int kr = jb & 1 ? 5000 : -1687, kg = jb & 1 ? -4187 : -3313, kb = jb & 1 ? -813 : 5000;
+        const int cBG = jb & 1 ? pack16(-813, -4187) : pack16(5000, -3313), cR = jb & 1 ? pack16(5000, 0) : pack16(-1687, 0);
 
         for (int it = 0; it < 8; it++) {
             int mb, type;
@@ -283,7 +332,7 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
                 const uint4* s4 = reinterpret_cast<const uint4*>(S.raw + 2 * v * PITCH + mb * 48);
                 uint4 a = s4[0], b = s4[1], c4 = s4[2];
                 uint32_t w[12] = { a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w, c4.x, c4.y, c4.z, c4.w };
-                chroma_row(w, d, kr, kg, kb, jb & 1);
+                chroma_row(w, d, cBG, cR, jb & 1);
             }
             aan8(d[0], d[1], d[2], d[3], d[4], d[5], d[6], d[7]);                 // row pass
             __syncwarp();
@@ -300,18 +349,17 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
             for (int u = 0; u < 8; u++) flags |= quant_flag(d[u], gk[u], gc[u], gt[u], t[u]) ? (1u << u) : 0u;
             uint32_t q0 = __float_as_uint(t[0]);
             if (v == 0) {             // exact DC: d[0] is the integer sum of the 64 centred samples
-                const int q = quant_int(dc_coef_from_sum((int) d[0]), chroma ? 17 : 16);
+                const int cdc = dc_coef_from_sum((int) d[0]);
+                const int q = chroma ? quant_int(cdc, 17) : quant_int(cdc, 16);
                 q0 = (uint32_t) q;
                 flags &= ~1u;
                 if (active) S.dc[(mb + 1) * 6 + type] = q;
             }
             if (active) {
-                coefb[coef_byte(chunk, pos_lo & 0xff)] = (uint8_t) q0;
+                uint8_t* cb = coefb + chunk * 64;
+                cb[pos[0]] = (uint8_t) q0;
 #pragma unroll
-                for (int u = 1; u < 8; u++) {
-                    const uint32_t p = ((u < 4 ? pos_lo : pos_hi) >> (8 * (u & 3))) & 0xff;
-                    coefb[coef_byte(chunk, p)] = (uint8_t) __float_as_uint(t[u]);
-                }
+                for (int u = 1; u < 8; u++) cb[pos[u]] = (uint8_t) __float_as_uint(t[u]);
             } else {
                 flags = 0;
             }

@@ -128,3 +128,23 @@ def test_8k_decode_roundtrip(gpu, port):
     # lossy but close: PSNR of the round trip stays sane
     err = (dst.view(-1)[:: 97].float() - t.view(-1)[:: 97].float())
     assert float((err * err).mean()) < 120.0
+
+
+def test_every_colour_through_the_encoder(gpu, port):
+    """All 2^24 (R,G,B) triples pass through the encode kernel's own colour rows (dp2a numerators,
+    wide-multiply division, exact-multiple fallback): each colour sits once on an even/even pixel,
+    so it feeds luma AND both chroma samples.  8192x8192, whole payload against the oracle."""
+    import torch
+    w = h = 8192
+    stride = 3 * w
+    idx = torch.arange(1 << 24, dtype=torch.int32, device="cuda").view(4096, 4096)
+    rgb = torch.empty((h, w, 3), dtype=torch.uint8, device="cuda")
+    for dy, dx, mul in ((0, 0, 1), (0, 1, 65599), (1, 0, 2654435), (1, 1, 40503)):
+        c = (idx * mul) & 0xFFFFFF if mul != 1 else idx
+        rgb[dy::2, dx::2, 0] = ((c >> 16) & 255).to(torch.uint8)
+        rgb[dy::2, dx::2, 1] = ((c >> 8) & 255).to(torch.uint8)
+        rgb[dy::2, dx::2, 2] = (c & 255).to(torch.uint8)
+    rows = rgb.flip(0).flip(2).contiguous().view(-1)          # bottom-up, B,G,R
+    p, _ = _encode(gpu, rows, w, h, stride)
+    want = port.encode_bgr(rows.cpu().numpy(), w, h, stride)
+    assert p.cpu().numpy().tobytes() == want.tobytes()
