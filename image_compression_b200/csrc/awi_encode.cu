@@ -239,8 +239,10 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
     EncSmem& S = *reinterpret_cast<EncSmem*>(smem_raw);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
-    // ticketed tile order: a tile only ever waits on tiles whose CTAs already run
-    if (tid == 0) { S.tile = (int) atomicAdd(P.ticket, 1u); S.amb_count = 0; }
+    // single-pass mode: ticketed tile order, so a tile only ever waits on tiles whose CTAs already run.
+    // two-pass mode (staging buffer given): tiles are independent, any order will do.
+    const bool two_pass = P.stage != nullptr;
+    if (tid == 0) { S.tile = two_pass ? (int) blockIdx.x : (int) atomicAdd(P.ticket, 1u); S.amb_count = 0; }
     if (tid < 64) S.cosf[tid] = __uint_as_float(cos_bits_rt(tid));
     if (tid < 6) S.halo_sum[tid] = 0;
     S.amb[tid] = 0;
@@ -484,7 +486,44 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
         __syncthreads();
     }
 
-    // warp 0: decoupled look-back for the tile's payload offset, 4 descriptors per lane per round
+    const bool compact_ok = total + 16 <= COMPACT_CAP;
+    uint8_t* compact = reinterpret_cast<uint8_t*>(S.coef);
+
+    if (two_pass) {
+        // ---- two-pass tail: no tile waits for another.  Reserve room in the staging buffer (16-byte units,
+        // completion order), leave (where, how many bytes) for enc_scan_tiles / enc_gather_tiles.
+        if (tid == 0) {
+            const unsigned units = (total + 15u) >> 4;
+            const unsigned at = atomicAdd(P.stage_cursor, units);
+            S.tile_base = at;
+            P.tile_info[tile] = make_uint2(at, total);
+            if ((unsigned long long) at + units > P.stage_cap_units) atomicOr(P.err, 1u);
+        }
+        if (compact_ok) {
+            const uint8_t* src = S.raw + tid * SLOT;
+            uint8_t* dst = compact + my_off;
+            for (uint32_t i = 0; i < my_len; i++) dst[i] = src[i];
+        }
+        __syncthreads();
+        const unsigned long long at = S.tile_base;
+        const bool fits = at + ((total + 15u) >> 4) <= P.stage_cap_units;
+        if (P.chunk_off != nullptr && my_mb < n_mb)
+            P.chunk_off[(long long) (mb_first - P.mb0) * 6 + tid] = my_off;          // tile-relative; the gather pass adds the tile's offset
+        if (fits) {
+            uint8_t* out = P.stage + at * 16;
+            if (compact_ok) {
+                const uint4* c4 = reinterpret_cast<const uint4*>(compact);
+                uint4* o4 = reinterpret_cast<uint4*>(out);
+                for (uint32_t j = tid; j < ((total + 15u) >> 4); j += THREADS) o4[j] = c4[j];
+            } else {                                     // oversized tile (> 64 B per chunk on average): chunk by chunk
+                const uint8_t* src = S.raw + tid * SLOT;
+                for (uint32_t i = 0; i < my_len; i++) out[my_off + i] = src[i];
+            }
+        }
+        return;
+    }
+
+    // ---- single-pass tail.  warp 0: decoupled look-back for the tile's payload offset, 4 descriptors per lane per round
     if (warp == 0) {
         constexpr unsigned long long FLAG_AGG = 1ull << 62, FLAG_PFX = 2ull << 62, VMASK = (1ull << 62) - 1;
         unsigned long long excl = 0;
@@ -527,15 +566,10 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
         }
     }
     // meanwhile / afterwards: every thread moves its own chunk to its place in the compacted tile
-    const bool compact_ok = total + 4 <= COMPACT_CAP;
-    uint8_t* compact = reinterpret_cast<uint8_t*>(S.coef);
     if (compact_ok) {
         const uint8_t* src = S.raw + tid * SLOT;
         uint8_t* dst = compact + my_off;
         for (uint32_t i = 0; i < my_len; i++) dst[i] = src[i];
-    } else {
-        S.len[tid] = my_len;
-        S.off[tid] = my_off;
     }
     __syncthreads();
 
@@ -561,15 +595,77 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
             }
             const uint32_t tail0 = head + (n_words << 2);
             if (tail0 + tid < total) out[tail0 + tid] = compact[tail0 + tid];
-        } else if (fits) {                              // oversized tile (> 64 B per chunk on average): direct scatter
-            for (int j = 0; j < 32; j++) {
-                const int c = (warp << 5) + j;
-                const uint32_t Lj = S.len[c], Oj = S.off[c];
-                const uint8_t* src = S.raw + c * SLOT;
-                uint8_t* dst = P.out + base + Oj;
-                for (uint32_t i = lane; i < Lj; i += 32) dst[i] = src[i];
-            }
+        } else if (fits) {                              // oversized tile: chunk by chunk
+            const uint8_t* src = S.raw + tid * SLOT;
+            uint8_t* dst = P.out + base + my_off;
+            for (uint32_t i = 0; i < my_len; i++) dst[i] = src[i];
         }
+    }
+}
+
+// ---------------------------------------------------------------- two-pass mode, passes 2 and 3
+// Exclusive scan of the tiles' byte counts in tile order (one CTA; a few ten thousand tiles).
+__global__ void __launch_bounds__(1024) enc_scan_tiles(const uint2* __restrict__ tile_info, int n_tiles,
+                                                       unsigned long long* __restrict__ tile_off,
+                                                       unsigned long long* __restrict__ out_len,
+                                                       unsigned long long out_cap, unsigned int* err) {
+    __shared__ unsigned long long wsum[32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int per = (n_tiles + 1023) / 1024;
+    const int t0 = min(n_tiles, tid * per), t1 = min(n_tiles, t0 + per);
+    unsigned long long mine = 0;
+    for (int t = t0; t < t1; t++) mine += tile_info[t].y;
+    unsigned long long incl = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        unsigned long long v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += v;
+    }
+    if (lane == 31) wsum[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+        unsigned long long w = wsum[lane], wi = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            unsigned long long v = __shfl_up_sync(0xffffffffu, wi, o);
+            if (lane >= o) wi += v;
+        }
+        wsum[lane] = wi - w;
+        if (lane == 31) {
+            *out_len = wi;
+            if (wi > out_cap) atomicOr(err, 1u);
+        }
+    }
+    __syncthreads();
+    unsigned long long run = wsum[warp] + incl - mine;
+    for (int t = t0; t < t1; t++) { tile_off[t] = run; run += tile_info[t].y; }
+}
+
+// One warp per tile: staging (16-byte aligned, completion order) -> payload (byte offsets, tile order).
+__global__ void __launch_bounds__(256) enc_gather_tiles(const uint8_t* __restrict__ stage, const uint2* __restrict__ tile_info,
+                                                        const unsigned long long* __restrict__ tile_off, int n_tiles,
+                                                        uint8_t* __restrict__ out, const unsigned long long* __restrict__ out_len,
+                                                        unsigned long long out_cap, uint32_t* __restrict__ chunk_off,
+                                                        long long n_chunks) {
+    const int tile = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (tile >= n_tiles || *out_len > out_cap) return;
+    const uint2 info = tile_info[tile];
+    const unsigned long long off = tile_off[tile];
+    const uint32_t total = info.y;
+    const uint8_t* src = stage + (unsigned long long) info.x * 16;
+    uint8_t* dst = out + off;
+    const uint32_t head = min(total, (uint32_t) ((4 - (reinterpret_cast<uintptr_t>(dst) & 3)) & 3));
+    if (lane < head) dst[lane] = src[lane];
+    const uint32_t n_words = (total - head) >> 2;
+    const uint32_t* sw = reinterpret_cast<const uint32_t*>(src);
+    uint32_t* dw = reinterpret_cast<uint32_t*>(dst + head);
+    const uint32_t sh = head * 8;
+    for (uint32_t j = lane; j < n_words; j += 32) dw[j] = __funnelshift_r(sw[j], sw[j + 1], sh);
+    const uint32_t tail0 = head + (n_words << 2);
+    if (tail0 + lane < total) dst[tail0 + lane] = src[tail0 + lane];
+    if (chunk_off != nullptr) {
+        const long long c0 = (long long) tile * (TILE_MB * 6);
+        for (int i = lane; i < TILE_MB * 6 && c0 + i < n_chunks; i += 32) chunk_off[c0 + i] += (uint32_t) off;
     }
 }
 
@@ -590,6 +686,12 @@ cudaError_t launch_encode(const EncParams& P, int n_tiles, cudaStream_t stream) 
         attr_set[dev] = true;
     }
     awi_encode_kernel<<<n_tiles, THREADS, sizeof(EncSmem), stream>>>(P);
+    if (P.stage != nullptr) {
+        const long long n_chunks = (long long) (P.mb1 - P.mb0) * 6;
+        enc_scan_tiles<<<1, 1024, 0, stream>>>(P.tile_info, n_tiles, P.tile_off, P.out_len, P.out_cap, P.err);
+        enc_gather_tiles<<<(n_tiles + 7) / 8, 256, 0, stream>>>(P.stage, P.tile_info, P.tile_off, n_tiles, P.out, P.out_len,
+                                                                 P.out_cap, P.chunk_off, n_chunks);
+    }
     return cudaGetLastError();
 }
 

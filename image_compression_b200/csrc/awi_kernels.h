@@ -39,8 +39,16 @@ struct EncParams {
     uint8_t* out;                 // payload bytes for this range
     unsigned long long out_cap;
     unsigned long long* out_len;  // payload length, written by the last tile
+    // single-pass mode (stage == nullptr): decoupled look-back
     unsigned long long* desc;     // one look-back descriptor per tile, zeroed before launch
     unsigned int* ticket;         // zeroed before launch
+    // two-pass mode (stage != nullptr): tiles land in a staging buffer in completion order, then
+    // enc_scan_tiles + enc_gather_tiles move them to their payload offsets
+    uint8_t* stage;               // 16-byte aligned
+    unsigned long long stage_cap_units;   // capacity in 16-byte units
+    unsigned int* stage_cursor;   // zeroed before launch
+    uint2* tile_info;             // per tile: (staging offset in units, bytes)
+    unsigned long long* tile_off; // per tile: payload offset
     unsigned int* err;            // bit 0: out_cap too small
     uint32_t* chunk_off;          // optional: byte offset of every chunk in `out`
     int8_t* qcoef;                // optional: quantised coefficients, 64 per chunk, scan order

@@ -39,7 +39,7 @@ bool fail(const char* fmt, ...) {
         if (e__ != cudaSuccess) return fail("%s failed: %s", #call, cudaGetErrorString(e__));     \
     } while (0)
 
-constexpr size_t ENC_WS_HEADER = 256;     // [0,8) payload length, [8,12) tile ticket
+constexpr size_t ENC_WS_HEADER = 256;     // [0,8) payload length, [8,12) tile ticket, [16,20) staging cursor
 
 struct Buf {
     uint8_t* p = nullptr;
@@ -49,7 +49,7 @@ struct Buf {
 struct Ctx {
     int dev = -1;
     cudaStream_t stream = nullptr;
-    Buf enc_ws, dec_ws, in, out;
+    Buf enc_ws, enc_stage, dec_ws, in, out;
     unsigned int* d_err = nullptr;
     uint64_t* h_len = nullptr;                // pinned
     std::mutex mu;
@@ -81,7 +81,7 @@ void destroy_ctx(Ctx* c) {
     if (!c) return;
     cudaSetDevice(c->dev);
     if (c->stream) cudaStreamDestroy(c->stream);
-    for (Buf* b : { &c->enc_ws, &c->dec_ws, &c->in, &c->out })
+    for (Buf* b : { &c->enc_ws, &c->enc_stage, &c->dec_ws, &c->in, &c->out })
         if (b->p) cudaFree(b->p);
     if (c->d_err) cudaFree(c->d_err);
     if (c->h_len) cudaFreeHost(c->h_len);
@@ -164,9 +164,12 @@ bool encode_dev_impl(Ctx* c, const uint8_t* d_rows, int width, int height, long 
     const long long n_mb = (long long) (r1 - r0) * mbw;
     const int n_tiles = (int) ((n_mb + awi::ENC_TILE_MB - 1) / awi::ENC_TILE_MB);
     CU(cudaSetDevice(c->dev));
-    const size_t ws_bytes = ENC_WS_HEADER + (size_t) n_tiles * 8;
-    if (!ensure(c->enc_ws, ws_bytes)) return false;
-    CU(cudaMemsetAsync(c->enc_ws.p, 0, ws_bytes, st));
+    // two-pass encode: tiles go to a staging buffer in completion order (no tile ever waits for
+    // another), then a scan + gather place them; scratch = header + (where,bytes) + offset per tile
+    const size_t ws_bytes = ENC_WS_HEADER + (size_t) n_tiles * 16;
+    const size_t stage_bytes = cap + (size_t) n_tiles * 16 + 256;
+    if (!ensure(c->enc_ws, ws_bytes) || !ensure(c->enc_stage, stage_bytes)) return false;
+    CU(cudaMemsetAsync(c->enc_ws.p, 0, ENC_WS_HEADER, st));
 
     awi::EncParams P{};
     // address of bottom-up row 0 of the full frame, had the whole frame been resident
@@ -182,7 +185,12 @@ bool encode_dev_impl(Ctx* c, const uint8_t* d_rows, int width, int height, long 
     P.out_cap = cap;
     P.out_len = reinterpret_cast<unsigned long long*>(c->enc_ws.p);
     P.ticket = reinterpret_cast<unsigned int*>(c->enc_ws.p + 8);
-    P.desc = reinterpret_cast<unsigned long long*>(c->enc_ws.p + ENC_WS_HEADER);
+    P.desc = nullptr;
+    P.stage = c->enc_stage.p;
+    P.stage_cap_units = (stage_bytes - 256) / 16;
+    P.stage_cursor = reinterpret_cast<unsigned int*>(c->enc_ws.p + 16);
+    P.tile_info = reinterpret_cast<uint2*>(c->enc_ws.p + ENC_WS_HEADER);
+    P.tile_off = reinterpret_cast<unsigned long long*>(c->enc_ws.p + ENC_WS_HEADER + (size_t) n_tiles * 8);
     P.err = c->d_err;
     P.chunk_off = d_chunk_off;
     P.qcoef = d_qcoef;
