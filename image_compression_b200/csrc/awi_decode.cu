@@ -452,7 +452,7 @@ size_t dec_workspace_bytes(unsigned long long payload_len, long long n_chunks) {
 }
 
 cudaError_t launch_decode(const DecParams& P, void* workspace, size_t workspace_bytes,
-                          const uint32_t* chunk_off_in, unsigned int* err, cudaStream_t stream) {
+                          const uint32_t* chunk_off_in, bool reuse_index, unsigned int* err, cudaStream_t stream) {
     const long long n_mb = (long long) P.mbw * P.mbh;
     const long long n_chunks = n_mb * 6;
     DecLayout Lo = dec_layout(P.payload_len, n_chunks);
@@ -460,7 +460,13 @@ cudaError_t launch_decode(const DecParams& P, void* workspace, size_t workspace_
     uint8_t* ws = static_cast<uint8_t*>(workspace);
     uint32_t* chunk_off = reinterpret_cast<uint32_t*>(ws + Lo.off_chunk_off);
 
-    if (chunk_off_in == nullptr) {
+    int* dcabs = reinterpret_cast<int*>(ws + Lo.off_dcabs);
+    int* tile_sum = reinterpret_cast<int*>(ws + Lo.off_tile_sum);
+    int* tile_base = reinterpret_cast<int*>(ws + Lo.off_tile_base);
+    if (reuse_index) {
+        // chunk offsets and DC values of this payload are already in the workspace (an earlier call on
+        // the same stream): only reconstruct another range of macroblock rows
+    } else if (chunk_off_in == nullptr) {
         uint8_t* Lg = ws + Lo.off_L;
         auto table = [&](int lv) { return reinterpret_cast<unsigned long long*>(ws + Lo.off_table[lv]); };
         auto state = [&](int lv) { return reinterpret_cast<NodeState*>(ws + Lo.off_state[lv]); };
@@ -483,12 +489,11 @@ cudaError_t launch_decode(const DecParams& P, void* workspace, size_t workspace_
         if (e != cudaSuccess) return e;
     }
 
-    int* dcabs = reinterpret_cast<int*>(ws + Lo.off_dcabs);
-    int* tile_sum = reinterpret_cast<int*>(ws + Lo.off_tile_sum);
-    int* tile_base = reinterpret_cast<int*>(ws + Lo.off_tile_base);
+    if (!reuse_index) {
     dec_dc_tile<0><<<(unsigned) Lo.n_dct, DCT_MB, 0, stream>>>(P.payload, chunk_off, n_mb, tile_sum, nullptr, nullptr, P.payload_len, err);
     dec_dc_scan_tiles<<<1, 1024, 0, stream>>>(tile_sum, Lo.n_dct, tile_base);
     dec_dc_tile<1><<<(unsigned) Lo.n_dct, DCT_MB, 0, stream>>>(P.payload, chunk_off, n_mb, nullptr, tile_base, dcabs, P.payload_len, err);
+    }
 
     static bool attr_set[64] = { false };
     int dev = 0;

@@ -608,6 +608,7 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
 __global__ void __launch_bounds__(1024) enc_scan_tiles(const uint2* __restrict__ tile_info, int n_tiles,
                                                        unsigned long long* __restrict__ tile_off,
                                                        unsigned long long* __restrict__ out_len,
+                                                       unsigned long long* __restrict__ chain,
                                                        unsigned long long out_cap, unsigned int* err) {
     __shared__ unsigned long long wsum[32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -630,10 +631,13 @@ __global__ void __launch_bounds__(1024) enc_scan_tiles(const uint2* __restrict__
             unsigned long long v = __shfl_up_sync(0xffffffffu, wi, o);
             if (lane >= o) wi += v;
         }
-        wsum[lane] = wi - w;
+        // chained calls (sub-stripes of one frame) continue where the previous call's payload ended
+        const unsigned long long base = chain != nullptr ? *chain : 0ull;
+        wsum[lane] = base + wi - w;
         if (lane == 31) {
-            *out_len = wi;
-            if (wi > out_cap) atomicOr(err, 1u);
+            *out_len = base + wi;
+            if (chain != nullptr) *chain = base + wi;
+            if (base + wi > out_cap) atomicOr(err, 1u);
         }
     }
     __syncthreads();
@@ -688,7 +692,7 @@ cudaError_t launch_encode(const EncParams& P, int n_tiles, cudaStream_t stream) 
     awi_encode_kernel<<<n_tiles, THREADS, sizeof(EncSmem), stream>>>(P);
     if (P.stage != nullptr) {
         const long long n_chunks = (long long) (P.mb1 - P.mb0) * 6;
-        enc_scan_tiles<<<1, 1024, 0, stream>>>(P.tile_info, n_tiles, P.tile_off, P.out_len, P.out_cap, P.err);
+        enc_scan_tiles<<<1, 1024, 0, stream>>>(P.tile_info, n_tiles, P.tile_off, P.out_len, P.chain, P.out_cap, P.err);
         enc_gather_tiles<<<(n_tiles + 7) / 8, 256, 0, stream>>>(P.stage, P.tile_info, P.tile_off, n_tiles, P.out, P.out_len,
                                                                  P.out_cap, P.chunk_off, n_chunks);
     }

@@ -49,6 +49,7 @@ struct EncParams {
     unsigned int* stage_cursor;   // zeroed before launch
     uint2* tile_info;             // per tile: (staging offset in units, bytes)
     unsigned long long* tile_off; // per tile: payload offset
+    unsigned long long* chain;    // optional in/out: payload offset to start at / ended at (sub-stripes of one frame)
     unsigned int* err;            // bit 0: out_cap too small
     uint32_t* chunk_off;          // optional: byte offset of every chunk in `out`
     int8_t* qcoef;                // optional: quantised coefficients, 64 per chunk, scan order
@@ -73,8 +74,9 @@ struct DecWorkspace {
 };
 size_t dec_workspace_bytes(unsigned long long payload_len, long long n_chunks);
 // chunk_off_in: optional encoder side-info (skips boundary discovery when non-null)
+// reuse_index: the workspace already holds this payload's chunk offsets and DCs (skip everything but reconstruct)
 cudaError_t launch_decode(const DecParams& P, void* workspace, size_t workspace_bytes,
-                          const uint32_t* chunk_off_in, unsigned int* err, cudaStream_t stream);
+                          const uint32_t* chunk_off_in, bool reuse_index, unsigned int* err, cudaStream_t stream);
 
 // ---- misc kernels (gpu_codec.cu)
 cudaError_t launch_synth(uint8_t* rows, int width, int height, long long stride, int kind, uint32_t seed,

@@ -39,6 +39,8 @@ bool fail(const char* fmt, ...) {
         if (e__ != cudaSuccess) return fail("%s failed: %s", #call, cudaGetErrorString(e__));     \
     } while (0)
 
+constexpr int MAX_SUB = 32;               // sub-stripes a frame is cut into to overlap PCIe copies with the kernels
+constexpr size_t SUB_BYTES = 48u << 20;   // aim for ~48 MB of pixels per sub-stripe
 constexpr size_t ENC_WS_HEADER = 256;     // [0,8) payload length, [8,12) tile ticket, [16,20) staging cursor
 
 struct Buf {
@@ -48,9 +50,12 @@ struct Buf {
 
 struct Ctx {
     int dev = -1;
-    cudaStream_t stream = nullptr;
+    cudaStream_t stream = nullptr;            // compute (and small copies)
+    cudaStream_t copy_stream = nullptr;       // bulk H2D / D2H overlapped with compute
+    cudaEvent_t ev[MAX_SUB] = { nullptr };
     Buf enc_ws, enc_stage, dec_ws, in, out;
     unsigned int* d_err = nullptr;
+    unsigned long long* d_run = nullptr;      // running payload offset of a frame encoded in sub-stripes
     uint64_t* h_len = nullptr;                // pinned
     std::mutex mu;
 };
@@ -81,11 +86,62 @@ void destroy_ctx(Ctx* c) {
     if (!c) return;
     cudaSetDevice(c->dev);
     if (c->stream) cudaStreamDestroy(c->stream);
+    if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
+    for (cudaEvent_t e : c->ev) if (e) cudaEventDestroy(e);
+    if (c->d_run) cudaFree(c->d_run);
     for (Buf* b : { &c->enc_ws, &c->enc_stage, &c->dec_ws, &c->in, &c->out })
         if (b->p) cudaFree(b->p);
     if (c->d_err) cudaFree(c->d_err);
     if (c->h_len) cudaFreeHost(c->h_len);
     delete c;
+}
+
+bool make_events(Ctx* c) {
+    for (int i = 0; i < MAX_SUB; i++)
+        if (cudaEventCreateWithFlags(&c->ev[i], cudaEventDisableTiming) != cudaSuccess) return false;
+    return true;
+}
+
+// Result buffers handed to the caller (`*payload`) come from a small pool of page-locked
+// blocks so the device->host copy runs at full PCIe speed and no page is pinned per call.
+// gpu_codec_free() puts a block back; anything not from the pool goes to free().
+struct PinnedBlock { void* p; size_t cap; bool in_use; };
+std::vector<PinnedBlock> g_pool;
+std::mutex g_pool_mu;
+
+void* pool_get(size_t bytes) {
+    std::lock_guard<std::mutex> lk(g_pool_mu);
+    if (bytes == 0) bytes = 1;
+    for (PinnedBlock& b : g_pool)
+        if (!b.in_use && b.cap >= bytes && b.cap <= 4 * bytes + (1u << 20)) { b.in_use = true; return b.p; }
+    void* p = nullptr;
+    const size_t cap = bytes + bytes / 4 + 4096;
+    if (cudaMallocHost(&p, cap) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    g_pool.push_back({ p, cap, true });
+    return p;
+}
+
+bool pool_put(void* p) {           // true if p was a pool block
+    std::lock_guard<std::mutex> lk(g_pool_mu);
+    size_t idle = 0;
+    for (PinnedBlock& b : g_pool) if (!b.in_use) idle += b.cap;
+    for (size_t i = 0; i < g_pool.size(); i++)
+        if (g_pool[i].p == p) {
+            if (idle > (1ull << 30)) {             // do not hoard more than 1 GB of idle pinned memory
+                cudaFreeHost(p);
+                g_pool.erase(g_pool.begin() + (long) i);
+            } else {
+                g_pool[i].in_use = false;
+            }
+            return true;
+        }
+    return false;
+}
+
+void pool_trim() {
+    std::lock_guard<std::mutex> lk(g_pool_mu);
+    for (size_t i = 0; i < g_pool.size();)
+        if (!g_pool[i].in_use) { cudaFreeHost(g_pool[i].p); g_pool.erase(g_pool.begin() + (long) i); } else i++;
 }
 
 inline int align_of(const void* p, long long stride) {
@@ -150,7 +206,7 @@ __global__ void colour_kernel(const uint8_t* in, size_t n, int inverse, uint8_t*
 
 bool encode_dev_impl(Ctx* c, const uint8_t* d_rows, int width, int height, long long stride, int wy0, int wy1,
                      int r0, int r1, uint8_t* d_payload, size_t cap, uint64_t* d_len, uint32_t* d_chunk_off,
-                     int8_t* d_qcoef, cudaStream_t st) {
+                     int8_t* d_qcoef, cudaStream_t st, unsigned long long* d_chain = nullptr) {
     if (width <= 0 || height <= 0) return fail("encode: bad geometry %dx%d", width, height);
     if (stride < 3ll * width) return fail("encode: row_stride %lld < 3*width", stride);
     const int mbw = (width + 15) / 16, mbh = (height + 15) / 16;
@@ -191,6 +247,7 @@ bool encode_dev_impl(Ctx* c, const uint8_t* d_rows, int width, int height, long 
     P.stage_cursor = reinterpret_cast<unsigned int*>(c->enc_ws.p + 16);
     P.tile_info = reinterpret_cast<uint2*>(c->enc_ws.p + ENC_WS_HEADER);
     P.tile_off = reinterpret_cast<unsigned long long*>(c->enc_ws.p + ENC_WS_HEADER + (size_t) n_tiles * 8);
+    P.chain = d_chain;
     P.err = c->d_err;
     P.chunk_off = d_chunk_off;
     P.qcoef = d_qcoef;
@@ -200,7 +257,8 @@ bool encode_dev_impl(Ctx* c, const uint8_t* d_rows, int width, int height, long 
 }
 
 bool decode_dev_impl(Ctx* c, const uint8_t* d_payload, size_t len, int width, int height, int r0, int r1,
-                     uint8_t* d_dst, long long stride, int rgb, const uint32_t* d_chunk_off, cudaStream_t st) {
+                     uint8_t* d_dst, long long stride, int rgb, const uint32_t* d_chunk_off, cudaStream_t st,
+                     bool reuse_index = false) {
     if (width <= 0 || height <= 0) return fail("decode: bad geometry %dx%d", width, height);
     const int mbw = (width + 15) / 16, mbh = (height + 15) / 16;
     if (r0 < 0 || r1 > mbh || r0 > r1) return fail("decode: bad macroblock row range [%d,%d) of %d", r0, r1, mbh);
@@ -224,7 +282,7 @@ bool decode_dev_impl(Ctx* c, const uint8_t* d_payload, size_t len, int width, in
     P.dst = d_dst;
     P.stride = stride;
     P.rgb_topdown = rgb ? 1 : 0;
-    CU(awi::launch_decode(P, c->dec_ws.p, c->dec_ws.bytes, d_chunk_off, c->d_err, st));
+    CU(awi::launch_decode(P, c->dec_ws.p, c->dec_ws.bytes, d_chunk_off, reuse_index, c->d_err, st));
     return true;
 }
 
@@ -280,6 +338,8 @@ bool gpu_codec_init_devices(const int* ids, int n) {
         c->dev = ids[i];
         g_ctx.push_back(c);
         if (cudaSetDevice(c->dev) != cudaSuccess || cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess ||
+            cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking) != cudaSuccess ||
+            cudaMalloc(&c->d_run, 8) != cudaSuccess || !make_events(c) ||
             cudaMalloc(&c->d_err, 4) != cudaSuccess || cudaMemset(c->d_err, 0, 4) != cudaSuccess ||
             cudaMallocHost(&c->h_len, 64) != cudaSuccess) {
             cudaError_t e = cudaGetLastError();
@@ -302,6 +362,7 @@ void gpu_codec_shutdown(void) {
     std::lock_guard<std::mutex> lk(g_mu);
     for (Ctx* c : g_ctx) destroy_ctx(c);
     g_ctx.clear();
+    pool_trim();
 }
 
 const char* gpu_codec_last_error(void) { return g_last_error.c_str(); }
@@ -317,7 +378,7 @@ void* gpu_codec_host_alloc(size_t bytes) {
     return p;
 }
 void gpu_codec_host_free(void* p) { if (p) cudaFreeHost(p); }
-void gpu_codec_free(void* p) { free(p); }
+void gpu_codec_free(void* p) { if (p && !pool_put(p)) free(p); }
 
 // ------------------------------------------------------------------ device-resident
 
@@ -373,6 +434,43 @@ bool gpu_codec_selftest_colour_dev(int ctx, const uint8_t* d_in, size_t n, int i
 
 // ------------------------------------------------------------------ host-buffer paths
 
+// Encode macroblock rows [R0,R1) of a host frame on context c, leaving the payload in c->out and
+// its length in *c->h_len after the compute stream drains.  The stripe's pixel rows are copied in
+// sub-stripes on the copy stream; each sub-stripe's kernels start as soon as its rows (and the
+// halo rows above them) have landed, so the PCIe transfer hides the compute.
+static bool encode_stripe_async(Ctx* c, const uint8_t* bmp_rows, int width, int height, int row_stride, int R0, int R1) {
+    const int mbw = (width + 15) / 16;
+    const int y_lo = R0 > 0 ? 16 * R0 - 16 : 0, y_hi = 16 * R1 < height ? 16 * R1 : height;
+    const size_t in_bytes = (size_t) (y_hi - y_lo) * row_stride;
+    const size_t cap = (size_t) (R1 - R0) * mbw * 6 * 121 + 16;
+    CU(cudaSetDevice(c->dev));
+    if (!ensure(c->in, in_bytes) || !ensure(c->out, cap)) return false;
+    int n_sub = (int) ((in_bytes + SUB_BYTES - 1) / SUB_BYTES);
+    if (n_sub > MAX_SUB) n_sub = MAX_SUB;
+    if (n_sub > R1 - R0) n_sub = R1 - R0;
+    if (n_sub < 1) n_sub = 1;
+    CU(cudaMemsetAsync(c->d_run, 0, 8, c->stream));
+    int y_done = y_lo;                                   // rows [y_lo, y_done) are on their way
+    for (int s = 0; s < n_sub; s++) {
+        const int r0 = R0 + (int) ((long long) (R1 - R0) * s / n_sub), r1 = R0 + (int) ((long long) (R1 - R0) * (s + 1) / n_sub);
+        const int y_to = 16 * r1 < height ? 16 * r1 : height;
+        if (y_to > y_done) {
+            // rows y_done..y_to-1 are the bottom-up byte range [(height-y_to)*stride, (height-y_done)*stride)
+            const uint8_t* hsrc = bmp_rows + (size_t) (height - y_to) * row_stride;
+            uint8_t* ddst = c->in.p + (size_t) (y_hi - y_to) * row_stride;
+            CU(cudaMemcpyAsync(ddst, hsrc, (size_t) (y_to - y_done) * row_stride, cudaMemcpyHostToDevice, c->copy_stream));
+            y_done = y_to;
+        }
+        CU(cudaEventRecord(c->ev[s], c->copy_stream));
+        CU(cudaStreamWaitEvent(c->stream, c->ev[s], 0));
+        if (!encode_dev_impl(c, c->in.p, width, height, row_stride, y_lo, y_hi, r0, r1, c->out.p, cap, nullptr, nullptr,
+                             nullptr, c->stream, c->d_run))
+            return false;
+    }
+    CU(cudaMemcpyAsync(c->h_len, c->d_run, 8, cudaMemcpyDeviceToHost, c->stream));
+    return true;
+}
+
 bool gpu_codec_encode_bgr(const uint8_t* bmp_rows, int width, int height, int row_stride, uint8_t** payload,
                           size_t* payload_len) {
     if (!payload || !payload_len) return fail("encode: null output argument");
@@ -380,26 +478,16 @@ bool gpu_codec_encode_bgr(const uint8_t* bmp_rows, int width, int height, int ro
     *payload_len = 0;
     if (g_ctx.empty()) return fail("encode: not initialised (call gpu_codec_init)");
     if (!bmp_rows || width <= 0 || height <= 0 || row_stride < 3 * width) return fail("encode: bad arguments");
-    const int mbw = (width + 15) / 16, mbh = (height + 15) / 16;
+    const int mbh = (height + 15) / 16;
     const int G = (int) g_ctx.size() < mbh ? (int) g_ctx.size() : mbh;
     std::vector<std::unique_lock<std::mutex>> locks;
     for (int g = 0; g < G; g++) locks.emplace_back(g_ctx[g]->mu);
 
-    // phase 1: every GPU gets its stripe (+ the macroblock row above it), encodes it
+    // phase 1: every GPU gets its stripe (+ the macroblock row above it) and encodes it
     for (int g = 0; g < G; g++) {
-        Ctx* c = g_ctx[g];
         int r0, r1;
         stripe_rows(mbh, g, G, r0, r1);
-        const int y_lo = r0 > 0 ? 16 * r0 - 16 : 0, y_hi = 16 * r1 < height ? 16 * r1 : height;
-        const size_t in_bytes = (size_t) (y_hi - y_lo) * row_stride;
-        const size_t cap = (size_t) (r1 - r0) * mbw * 6 * 121 + 16;
-        CU(cudaSetDevice(c->dev));
-        if (!ensure(c->in, in_bytes) || !ensure(c->out, cap)) return false;
-        CU(cudaMemcpyAsync(c->in.p, bmp_rows + (size_t) (height - y_hi) * row_stride, in_bytes, cudaMemcpyHostToDevice, c->stream));
-        if (!encode_dev_impl(c, c->in.p, width, height, row_stride, y_lo, y_hi, r0, r1, c->out.p, cap, nullptr, nullptr,
-                             nullptr, c->stream))
-            return false;
-        CU(cudaMemcpyAsync(c->h_len, c->enc_ws.p, 8, cudaMemcpyDeviceToHost, c->stream));
+        if (!encode_stripe_async(g_ctx[g], bmp_rows, width, height, row_stride, r0, r1)) return false;
     }
     // phase 2: exclusive prefix sum of the per-stripe byte lengths, stitch (byte seams)
     size_t total = 0;
@@ -410,18 +498,18 @@ bool gpu_codec_encode_bgr(const uint8_t* bmp_rows, int width, int height, int ro
         len[g] = (size_t) *g_ctx[g]->h_len;
         total += len[g];
     }
-    uint8_t* buf = static_cast<uint8_t*>(malloc(total ? total : 1));
-    if (!buf) return fail("encode: out of host memory (%zu bytes)", total);
+    uint8_t* buf = static_cast<uint8_t*>(pool_get(total));
+    if (!buf) return fail("encode: out of page-locked host memory (%zu bytes)", total);
     for (int g = 0; g < G; g++) {
         Ctx* c = g_ctx[g];
         cudaSetDevice(c->dev);
         cudaError_t e = cudaMemcpyAsync(buf + off[g], c->out.p, len[g], cudaMemcpyDeviceToHost, c->stream);
-        if (e != cudaSuccess) { free(buf); return fail("encode: D2H failed: %s", cudaGetErrorString(e)); }
+        if (e != cudaSuccess) { pool_put(buf); return fail("encode: D2H failed: %s", cudaGetErrorString(e)); }
     }
     for (int g = 0; g < G; g++) {
         cudaSetDevice(g_ctx[g]->dev);
         cudaError_t e = cudaStreamSynchronize(g_ctx[g]->stream);
-        if (e != cudaSuccess) { free(buf); return fail("encode: sync failed: %s", cudaGetErrorString(e)); }
+        if (e != cudaSuccess) { pool_put(buf); return fail("encode: sync failed: %s", cudaGetErrorString(e)); }
     }
     *payload = buf;
     *payload_len = total;
@@ -435,8 +523,7 @@ bool gpu_codec_encode_batch_bgr(const uint8_t* const* frames, int n_frames, int 
         return fail("encode_batch: bad arguments");
     for (int i = 0; i < n_frames; i++) { payloads[i] = nullptr; payload_lens[i] = 0; }
     const int G = (int) g_ctx.size();
-    const int mbw = (width + 15) / 16, mbh = (height + 15) / 16;
-    const size_t in_bytes = (size_t) height * row_stride, cap = (size_t) mbw * mbh * 6 * 121 + 16;
+    const int mbh = (height + 15) / 16;
     std::vector<std::string> errs(G);
     std::vector<std::thread> workers;
     for (int g = 0; g < G; g++) {
@@ -444,18 +531,12 @@ bool gpu_codec_encode_batch_bgr(const uint8_t* const* frames, int n_frames, int 
             Ctx* c = g_ctx[g];
             std::lock_guard<std::mutex> lk(c->mu);
             auto body = [&]() -> bool {
-                CU(cudaSetDevice(c->dev));
-                if (!ensure(c->in, in_bytes) || !ensure(c->out, cap)) return false;
                 for (int i = g; i < n_frames; i += G) {
-                    CU(cudaMemcpyAsync(c->in.p, frames[i], in_bytes, cudaMemcpyHostToDevice, c->stream));
-                    if (!encode_dev_impl(c, c->in.p, width, height, row_stride, 0, height, 0, mbh, c->out.p, cap, nullptr,
-                                         nullptr, nullptr, c->stream))
-                        return false;
-                    CU(cudaMemcpyAsync(c->h_len, c->enc_ws.p, 8, cudaMemcpyDeviceToHost, c->stream));
+                    if (!encode_stripe_async(c, frames[i], width, height, row_stride, 0, mbh)) return false;
                     if (!check_err(c, c->stream, "encode_batch")) return false;
-                    size_t n = (size_t) *c->h_len;
-                    payloads[i] = static_cast<uint8_t*>(malloc(n ? n : 1));
-                    if (!payloads[i]) return fail("encode_batch: out of host memory");
+                    const size_t n = (size_t) *c->h_len;
+                    payloads[i] = static_cast<uint8_t*>(pool_get(n));
+                    if (!payloads[i]) return fail("encode_batch: out of page-locked host memory");
                     payload_lens[i] = n;
                     CU(cudaMemcpyAsync(payloads[i], c->out.p, n, cudaMemcpyDeviceToHost, c->stream));
                     CU(cudaStreamSynchronize(c->stream));
@@ -468,7 +549,7 @@ bool gpu_codec_encode_batch_bgr(const uint8_t* const* frames, int n_frames, int 
     for (auto& t : workers) t.join();
     for (int g = 0; g < G; g++)
         if (!errs[g].empty()) {
-            for (int i = 0; i < n_frames; i++) { free(payloads[i]); payloads[i] = nullptr; payload_lens[i] = 0; }
+            for (int i = 0; i < n_frames; i++) { gpu_codec_free(payloads[i]); payloads[i] = nullptr; payload_lens[i] = 0; }
             return fail("%s", errs[g].c_str());
         }
     return true;
@@ -484,9 +565,9 @@ static bool decode_host(const uint8_t* payload, size_t len, int width, int heigh
     for (int g = 0; g < G; g++) locks.emplace_back(g_ctx[g]->mu);
     for (int g = 0; g < G; g++) {
         Ctx* c = g_ctx[g];
-        int r0, r1;
-        stripe_rows(mbh, g, G, r0, r1);
-        const int y_lo = 16 * r0, y_hi = 16 * r1 < height ? 16 * r1 : height;
+        int R0, R1;
+        stripe_rows(mbh, g, G, R0, R1);
+        const int y_lo = 16 * R0, y_hi = 16 * R1 < height ? 16 * R1 : height;
         const size_t out_bytes = (size_t) (y_hi - y_lo) * pitch;
         CU(cudaSetDevice(c->dev));
         if (!ensure(c->in, len + 16) || !ensure(c->out, out_bytes)) return false;
@@ -494,18 +575,34 @@ static bool decode_host(const uint8_t* payload, size_t len, int width, int heigh
         // the stripe's rows are contiguous in both sinks; hand the kernel the address the
         // full frame's first byte would have
         uint8_t* vbase = rgb ? c->out.p - (long long) y_lo * pitch : c->out.p - (long long) (height - y_hi) * pitch;
-        if (!decode_dev_impl(c, c->in.p, len, width, height, r0, r1, vbase, pitch, rgb, nullptr, c->stream)) return false;
-        uint8_t* hdst = rgb ? dst + (size_t) y_lo * pitch : dst + (size_t) (height - y_hi) * pitch;
-        if (pitch == 3ll * width) {
-            CU(cudaMemcpyAsync(hdst, c->out.p, out_bytes, cudaMemcpyDeviceToHost, c->stream));
-        } else {   // leave the caller's row padding bytes alone
-            CU(cudaMemcpy2DAsync(hdst, (size_t) pitch, c->out.p, (size_t) pitch, (size_t) 3 * width, (size_t) (y_hi - y_lo),
-                                 cudaMemcpyDeviceToHost, c->stream));
+        int n_sub = (int) ((out_bytes + SUB_BYTES - 1) / SUB_BYTES);
+        if (n_sub > MAX_SUB) n_sub = MAX_SUB;
+        if (n_sub > R1 - R0) n_sub = R1 - R0;
+        if (n_sub < 1) n_sub = 1;
+        for (int s = 0; s < n_sub; s++) {
+            // parse once (first call), then reconstruct sub-stripes and ship each while the next one runs
+            const int r0 = R0 + (int) ((long long) (R1 - R0) * s / n_sub), r1 = R0 + (int) ((long long) (R1 - R0) * (s + 1) / n_sub);
+            if (!decode_dev_impl(c, c->in.p, len, width, height, r0, r1, vbase, pitch, rgb, nullptr, c->stream, s > 0)) return false;
+            CU(cudaEventRecord(c->ev[s], c->stream));
+            CU(cudaStreamWaitEvent(c->copy_stream, c->ev[s], 0));
+            const int ya = 16 * r0, yb = 16 * r1 < height ? 16 * r1 : height;
+            const size_t rel = rgb ? (size_t) (ya - y_lo) * pitch : (size_t) (y_hi - yb) * pitch;      // offset inside the stripe buffer
+            uint8_t* hdst = rgb ? dst + (size_t) ya * pitch : dst + (size_t) (height - yb) * pitch;
+            if (pitch == 3ll * width) {
+                CU(cudaMemcpyAsync(hdst, c->out.p + rel, (size_t) (yb - ya) * pitch, cudaMemcpyDeviceToHost, c->copy_stream));
+            } else {   // leave the caller's row padding bytes alone
+                CU(cudaMemcpy2DAsync(hdst, (size_t) pitch, c->out.p + rel, (size_t) pitch, (size_t) 3 * width, (size_t) (yb - ya),
+                                     cudaMemcpyDeviceToHost, c->copy_stream));
+            }
         }
     }
-    for (int g = 0; g < G; g++)
-        if (!check_err(g_ctx[g], g_ctx[g]->stream, "decode")) return false;
-    return true;
+    bool ok = true;
+    for (int g = 0; g < G; g++) {
+        if (!check_err(g_ctx[g], g_ctx[g]->stream, "decode")) ok = false;
+        cudaSetDevice(g_ctx[g]->dev);
+        if (cudaStreamSynchronize(g_ctx[g]->copy_stream) != cudaSuccess) ok = fail("decode: D2H failed");
+    }
+    return ok;
 }
 
 bool gpu_codec_decode_to_bgr(const uint8_t* payload, size_t len, int width, int height, uint8_t* bmp_rows, int row_stride) {
