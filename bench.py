@@ -245,7 +245,7 @@ def run_ours(args, width, height, frames_per_rank, workload_desc) -> dict | None
 
     # roofline of the fused encode kernel (the only kernel in the step)
     peak, peak_src = peaks()
-    launches = args.steps * frames_per_rank
+    launches = args.steps * frames_per_rank * 3          # awi_encode_kernel + enc_scan_tiles + enc_gather_tiles per frame
     alg_bytes = 3 * width * height + payload_bytes               # per launch (last frame's payload; frames are alike)
     kernel_ms = ms / launches
     achieved = alg_bytes / (kernel_ms * 1e-3) / 1e9

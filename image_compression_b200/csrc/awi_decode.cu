@@ -239,11 +239,12 @@ __global__ void __launch_bounds__(1024) dec_dc_scan_tiles(const int* __restrict_
 }
 
 // ---------------------------------------------------------------- 6: reconstruct
-struct RecSmem {
-    int coef[REC_MB * 6][64];                 // dequantised coefficients, natural [u][v] order
+struct __align__(16) RecSmem {
+    int coef[REC_MB * 6][64];                 // dequantised coefficients, natural [u][v] order (only masked entries are valid)
     unsigned long long mask[REC_MB * 6];      // non-zero positions, natural order
-    double cosd[64];                          // (double) of the reference's fp32 table
-    uint8_t bytes[REC_MB * 6 * MAXCH + 16];   // the tile's slice of the payload
+    double cost[64];                          // cost[v*8 + x] = (double) cos_table[x][v]  (dct.c:14-23), frequency-major
+    double cucv[64];                          // cu*cv per natural position (dct.c:71-72,75)
+    uint32_t words[(REC_MB * 6 * MAXCH + 64) / 4];   // the tile's slice of the payload as big-endian words
     uint8_t yp[16][REC_MB * 16];
     uint8_t cbp[8][REC_MB * 8];
     uint8_t crp[8][REC_MB * 8];
@@ -274,19 +275,42 @@ __global__ void __launch_bounds__(REC_THREADS) dec_reconstruct(DecParams P, cons
     const int n_ch = n_mb * 6;
     if (*reinterpret_cast<volatile unsigned int*>(err) != 0) return;          // an earlier stage rejected the stream
 
-    // tables + zeroed coefficients
+    // the tile's chunks are contiguous in the stream: [b0, b1)
+    const uint32_t b0 = chunk_off[chunk0], b1 = chunk_off[chunk0 + n_ch];
+    uint32_t my_off = 0;
+    int my_dc = 0;
+    if (tid < n_ch) { my_off = chunk_off[chunk0 + tid]; my_dc = dcabs[chunk0 + tid]; }      // in flight during staging
+    if (b1 < b0 || b1 > P.payload_len || b1 - b0 > (uint32_t) (REC_MB * 6 * MAXCH)) { if (tid == 0) atomicOr(err, 4u); return; }
     if (tid < 64) {
-        S.cosd[tid] = (double) __uint_as_float(cos_bits_rt(tid));
+        const double c = (double) __uint_as_float(cos_bits_rt(tid));          // cos_table[x = tid>>3][v = tid&7]
+        S.cost[(tid & 7) * 8 + (tid >> 3)] = c;
+        const double inv_sqrt2 = 0.70710678118654746;
+        S.cucv[tid] = __dmul_rn((tid >> 3) == 0 ? inv_sqrt2 : 1.0, (tid & 7) == 0 ? inv_sqrt2 : 1.0);
         S.scan[tid] = (uint8_t) scan_rt(tid);
         S.q[0][tid] = (uint8_t) qluma_rt(tid);
         S.q[1][tid] = (uint8_t) qchroma_rt(tid);
     }
-    for (int i = tid; i < REC_MB * 6 * 64; i += REC_THREADS) (&S.coef[0][0])[i] = 0;
-    // the tile's chunks are contiguous in the stream
-    const uint32_t b0 = chunk_off[chunk0], b1 = chunk_off[chunk0 + n_ch];
-    if (b1 < b0 || b1 > P.payload_len) { if (tid == 0) atomicOr(err, 4u); return; }
+    // stage [a0, b1 + 8) as big-endian words, a0 = b0 rounded down to 4
+    const uint32_t a0 = b0 & ~3u;
     const uint32_t nbytes = min(b1 - b0, (uint32_t) (REC_MB * 6 * MAXCH));
-    for (uint32_t i = tid; i < nbytes + 4; i += REC_THREADS) S.bytes[i] = (b0 + i) < P.payload_len ? P.payload[b0 + i] : 0;
+    {
+        const uint32_t n_words = (b0 - a0 + nbytes + 8 + 3) >> 2;
+        const uint32_t* src = reinterpret_cast<const uint32_t*>(P.payload + a0);
+        const bool aligned = (reinterpret_cast<uintptr_t>(P.payload) & 3) == 0;
+        const uint32_t safe_words = (uint32_t) ((P.payload_len - a0) >> 2);   // whole words inside the buffer
+        for (uint32_t i = tid; i < n_words; i += REC_THREADS) {
+            uint32_t w = 0;
+            if (aligned && i < safe_words) {
+                w = __ldg(src + i);
+            } else {
+                for (int k = 0; k < 4; k++) {
+                    unsigned long long g = (unsigned long long) a0 + 4ull * i + k;
+                    if (g < P.payload_len) w |= (uint32_t) P.payload[g] << (8 * k);
+                }
+            }
+            S.words[i] = __byte_perm(w, 0, 0x0123);
+        }
+    }
     __syncthreads();
 
     // ---- parse: one thread per chunk (rle.c:113-170), dequantise (dct.c:128-145) and
@@ -294,37 +318,36 @@ __global__ void __launch_bounds__(REC_THREADS) dec_reconstruct(DecParams P, cons
     if (tid < n_ch) {
         const int type = tid % 6;
         const uint8_t* qt = S.q[type >= 4 ? 1 : 0];
-        const uint8_t* s = S.bytes + (chunk_off[chunk0 + tid] - b0);
-        const int limit_bits = (int) (nbytes - (chunk_off[chunk0 + tid] - b0)) * 8;
+        const uint32_t base_bit = (my_off - a0) * 8;                          // chunk start, in bits from S.words[0]
+        const int limit_bits = (int) (b1 - my_off) * 8;
         int* out = S.coef[tid];
         unsigned long long mask = 0;
-        int dc = dcabs[chunk0 + tid] * qt[0];
+        const int dc = my_dc * qt[0];
         out[0] = dc;
         if (dc != 0) mask |= 1ull;
         int bit = 12, idx = 1;
-        bool bad = false;
-        while (true) {
+        bool bad = my_off < b0 || my_off > b1;
+        while (!bad) {
             if (bit + 8 > limit_bits) { bad = true; break; }
-            int bi = bit >> 3;
-            uint32_t win = ((uint32_t) s[bi] << 24) | ((uint32_t) s[bi + 1] << 16) | ((uint32_t) s[bi + 2] << 8) | s[bi + 3];
-            win <<= (bit & 7);
-            int sym = win >> 24;
+            const uint32_t ab = base_bit + (uint32_t) bit;
+            const uint32_t win = __funnelshift_l(S.words[(ab >> 5) + 1], S.words[ab >> 5], ab & 31);   // 32 stream bits from `bit`
+            const int sym = win >> 24;
             if (sym == 0) break;
-            int run = sym >> 4, size = sym & 15;
+            const int run = sym >> 4, size = sym & 15;
             idx += run;
             if (idx > 63) { bad = true; break; }
             if (size > 0) {
-                int val = (int) ((win << 8) >> (32 - size));
-                int v = (val & (1 << (size - 1))) ? val : val - (1 << size) + 1;      // rle.c:152-155
-                int k = S.scan[idx];
-                int c = v * qt[k];
+                const int val = (int) ((win << 8) >> (32 - size));
+                const int v = (val & (1 << (size - 1))) ? val : val - (1 << size) + 1;      // rle.c:152-155
+                const int k = S.scan[idx];
+                const int c = v * qt[k];
                 out[k] = c;
                 if (c != 0) mask |= 1ull << k;
             }
             idx++;
             bit += 8 + size;
         }
-        if (bad) atomicOr(err, 4u);
+        if (bad) { atomicOr(err, 4u); mask = 0; }
         S.mask[tid] = mask;
     }
     __syncthreads();
@@ -338,28 +361,32 @@ __global__ void __launch_bounds__(REC_THREADS) dec_reconstruct(DecParams P, cons
 #pragma unroll
             for (int x = 0; x < 8; x++) sum[x] = 0.0;
             unsigned long long m = S.mask[blk];
-            const double inv_sqrt2 = 0.70710678118654746;
+            const int* cf = S.coef[blk];
             while (m) {
-                int k = __ffsll((long long) m) - 1;
+                const int k = __ffsll((long long) m) - 1;
                 m &= m - 1;
-                int u = k >> 3, v = k & 7;
-                double cu = u == 0 ? inv_sqrt2 : 1.0, cv = v == 0 ? inv_sqrt2 : 1.0;
-                double a = __dmul_rn(__dmul_rn(cu, cv), (double) S.coef[blk][k]);
-                double b = __dmul_rn(a, S.cosd[y * 8 + u]);
+                const int u = k >> 3, v = k & 7;
+                const double a = __dmul_rn(S.cucv[k], (double) cf[k]);
+                const double b = __dmul_rn(a, S.cost[u * 8 + y]);                             // cos_table[y][u]
+                const double2* cx = reinterpret_cast<const double2*>(&S.cost[v * 8]);          // cos_table[x][v], x = 0..7
 #pragma unroll
-                for (int x = 0; x < 8; x++) sum[x] = __dadd_rn(sum[x], __dmul_rn(b, S.cosd[x * 8 + v]));
+                for (int x2 = 0; x2 < 4; x2++) {
+                    const double2 c = cx[x2];
+                    sum[2 * x2] = __dadd_rn(sum[2 * x2], __dmul_rn(b, c.x));
+                    sum[2 * x2 + 1] = __dadd_rn(sum[2 * x2 + 1], __dmul_rn(b, c.y));
+                }
             }
             const int mb = blk / 6, type = blk - 6 * mb;
-            uint8_t px[8];
+            uint32_t px[8];
 #pragma unroll
-            for (int x = 0; x < 8; x++) px[x] = (uint8_t) clamp_trunc(__dadd_rn(__dmul_rn(0.25, sum[x]), 128.0));
+            for (int x = 0; x < 8; x++) px[x] = (uint32_t) clamp_trunc(__dadd_rn(__dmul_rn(0.25, sum[x]), 128.0));
             uint8_t* dstp;
             if (type < 4) dstp = &S.yp[((type >> 1) << 3) + y][mb * 16 + ((type & 1) << 3)];
             else if (type == 4) dstp = &S.cbp[y][mb * 8];
             else dstp = &S.crp[y][mb * 8];
             uint2 w;
-            w.x = px[0] | (px[1] << 8) | (px[2] << 16) | ((uint32_t) px[3] << 24);
-            w.y = px[4] | (px[5] << 8) | (px[6] << 16) | ((uint32_t) px[7] << 24);
+            w.x = px[0] | (px[1] << 8) | (px[2] << 16) | (px[3] << 24);
+            w.y = px[4] | (px[5] << 8) | (px[6] << 16) | (px[7] << 24);
             *reinterpret_cast<uint2*>(dstp) = w;
         }
     }

@@ -108,7 +108,16 @@ AWI_TABLE_FN(cos_bits, uint32_t, AWI_COS_BITS)
 // integer quotient equals the truncated fp64 value unless the numerator is an exact
 // multiple (then fp64 may land one ulp below the integer: 3464 / 0 / 688 of the 2^24
 // inputs).  Exact multiples take the literal fp64 expression.
-AWI_HD int clamp_trunc(double v) { return v > 255 ? 255 : (v < 0 ? 0 : (int) v); }
+AWI_HD int clamp_trunc(double v) {
+    // utils.c:10-17: >255 -> 255, <0 -> 0, else truncate.  Truncation first is equivalent: values above 255
+    // truncate to >= 255, values below 0 truncate to <= 0 (the conversion saturates far outside the int range).
+#if defined(__CUDA_ARCH__)
+    int i = __double2int_rz(v);
+#else
+    int i = v >= 2147483647.0 ? 2147483647 : (v <= -2147483648.0 ? (-2147483647 - 1) : (int) v);
+#endif
+    return i > 255 ? 255 : (i < 0 ? 0 : i);
+}
 
 AWI_HD int y_exact(int r, int g, int b) {
     return clamp_trunc(dadd_rn(dadd_rn(dmul_rn(0.299, (double) r), dmul_rn(0.587, (double) g)), dmul_rn(0.114, (double) b)));
@@ -158,12 +167,12 @@ AWI_HD int g_exact(int y, int cb, int cr) {
 AWI_HD int b_exact(int y, int cb) { return clamp_trunc(dadd_rn((double) y, dmul_rn(1.772, (double) (cb - 128)))); }
 
 AWI_HD int clamp_div(int n, int d, uint32_t magic, int shift, bool& exact_multiple) {
-    // n / d truncated and clamped to 0..255; d in {1000, 125000}
-    exact_multiple = false;
-    if (n <= 0) { exact_multiple = (n == 0); return 0; }
-    if (n >= 255 * d) { exact_multiple = (n == 255 * d); return 255; }
-    uint32_t q = umulhi32((uint32_t) n, magic) >> shift;
-    exact_multiple = ((uint32_t) n - q * (uint32_t) d) == 0u;
+    // n / d truncated and clamped to 0..255, branch-free; d in {1000, 125000}.  The multiply-high
+    // quotient is exact for 0 <= n <= 255*d and never too small beyond that, so min(.., 255) clamps.
+    const uint32_t nc = (uint32_t) (n < 0 ? 0 : n);
+    uint32_t q = umulhi32(nc, magic) >> shift;
+    q = q > 255u ? 255u : q;
+    exact_multiple = (nc - q * (uint32_t) d == 0u) && n >= 0;        // includes n == 0 and n == 255*d
     return (int) q;
 }
 AWI_HD int red_of(int y, int cr) {
