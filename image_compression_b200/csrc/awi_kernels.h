@@ -36,6 +36,8 @@ struct EncParams {
     int align;                    // 16, 4 or 1: guaranteed alignment of rows and stride
     int mbw;                      // macroblocks per row
     int mb0, mb1;                 // raster macroblock range [mb0, mb1) to encode
+    int sm_count;                 // filled by launch_encode
+    int n_tiles;                  // filled by launch_encode: tiles of ENC_TILE_MB macroblocks covering the range
     uint8_t* out;                 // payload bytes for this range
     unsigned long long out_cap;
     unsigned long long* out_len;  // payload length, written by the last tile
