@@ -211,9 +211,15 @@ def run_ours(args, width, height, frames_per_rank, workload_desc) -> dict | None
     plen = torch.zeros(1, dtype=torch.int64, device=dev)
     codec.sync_check(0)
 
+    batch_off = torch.zeros(n_res + 1, dtype=torch.int64, device=dev)
+    if n_res > 1:
+        payload = torch.empty(cap * n_res, dtype=torch.uint8, device=dev)
+
     def step():
-        for f in range(n_res):
-            codec.encode_dev(0, rows[f], width, height, stride, payload, plen)
+        if n_res == 1:
+            codec.encode_dev(0, rows[0], width, height, stride, payload, plen)
+        else:      # image-parallel batch: one set of launches for all resident frames
+            codec.encode_batch_dev(0, rows, n_res, frame_bytes, width, height, stride, payload, batch_off)
 
     def barrier():
         torch.cuda.synchronize()
@@ -224,7 +230,7 @@ def run_ours(args, width, height, frames_per_rank, workload_desc) -> dict | None
     for _ in range(max(args.warmup, 3)):
         step()
     codec.sync_check(0)
-    payload_bytes = int(plen.item())
+    payload_bytes = int(plen.item()) if n_res == 1 else int(batch_off[-1].item())
 
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
@@ -245,9 +251,9 @@ def run_ours(args, width, height, frames_per_rank, workload_desc) -> dict | None
 
     # roofline of the fused encode kernel (the only kernel in the step)
     peak, peak_src = peaks()
-    launches = args.steps * frames_per_rank * 3          # awi_encode_kernel + enc_scan_tiles + enc_gather_tiles per frame
-    alg_bytes = 3 * width * height + payload_bytes               # per launch (last frame's payload; frames are alike)
-    kernel_ms = ms / (args.steps * frames_per_rank)   # one encode step = awi_encode_kernel + tile scan + gather (the first is >95 %)
+    launches = args.steps * 3                            # awi_encode_kernel + enc_scan_tiles + enc_gather_tiles per step
+    alg_bytes = 3 * width * height * frames_per_rank + payload_bytes      # per step
+    kernel_ms = ms / args.steps   # one encode step = awi_encode_kernel + tile scan + gather (the first is >95 %)
     achieved = alg_bytes / (kernel_ms * 1e-3) / 1e9
     traffic = None
     tp = os.path.join(ROOT, "profiles", "ncu_traffic.json")
@@ -272,17 +278,34 @@ def run_ours(args, width, height, frames_per_rank, workload_desc) -> dict | None
     torch.from_numpy(host).copy_(rows[0])
     torch.cuda.synchronize()
     e2e_payload = 0
+    if frames_per_rank > 1:        # image-parallel batch through gpu_codec_encode_batch_bgr: all frames from pinned memory
+        hbatch = lib.gpu_codec_host_alloc(frame_bytes * frames_per_rank)
+        hb = np.ctypeslib.as_array(C.cast(hbatch, C.POINTER(C.c_uint8)), shape=(frames_per_rank, frame_bytes))
+        torch.from_numpy(hb).copy_(rows)
+        torch.cuda.synchronize()
+        ptrs = (C.c_void_p * frames_per_rank)(*[hbatch + f * frame_bytes for f in range(frames_per_rank)])
+        outs = (C.c_void_p * frames_per_rank)()
+        lens = (C.c_size_t * frames_per_rank)()
+
+        def e2e_step():
+            if not lib.gpu_codec_encode_batch_bgr(ptrs, frames_per_rank, width, height, stride, outs, lens):
+                raise SystemExit("bench.py: " + lib.gpu_codec_last_error().decode())
+            tot = sum(lens[i] for i in range(frames_per_rank))
+            for i in range(frames_per_rank):
+                lib.gpu_codec_free(C.c_void_p(outs[i]))
+            return tot
+    else:
+        def e2e_step():
+            addr, n = codec.encode_bgr_ptr(hptr, width, height, stride)
+            codec.free_payload(addr)
+            return n
     for _ in range(2):
-        addr, n = codec.encode_bgr_ptr(hptr, width, height, stride)
-        codec.free_payload(addr)
+        e2e_step()
     barrier()
     t0 = time.perf_counter()
     ev0.record()
     for _ in range(e2e_steps):
-        for _f in range(frames_per_rank):
-            addr, n = codec.encode_bgr_ptr(hptr, width, height, stride)
-            e2e_payload = n
-            codec.free_payload(addr)
+        e2e_payload = e2e_step()
     ev1.record()
     torch.cuda.synchronize()
     e2e_ms = max(ev0.elapsed_time(ev1), (time.perf_counter() - t0) * 1e3)
@@ -292,8 +315,8 @@ def run_ours(args, width, height, frames_per_rank, workload_desc) -> dict | None
     e2e_val = px_per_step * e2e_steps / (float(te.item()) * 1e-3) / 1e6
     lib.gpu_codec_host_free(C.c_void_p(hptr))
     e2e = {"value": round(e2e_val, 1), "unit": "Mpixel/s", "h2d_bytes_per_step": frame_bytes * frames_per_rank,
-           "d2h_bytes_per_step": (e2e_payload + 8) * frames_per_rank, "steps": e2e_steps,
-           "api": "gpu_codec_encode_bgr (pinned host buffers)"}
+           "d2h_bytes_per_step": e2e_payload + 8 * (frames_per_rank + 1), "steps": e2e_steps,
+           "api": ("gpu_codec_encode_bgr" if frames_per_rank == 1 else "gpu_codec_encode_batch_bgr") + " (pinned host buffers)"}
 
     extras = {}
     if rank == 0 and world == 1 and not args.no_extras:

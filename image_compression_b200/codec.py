@@ -33,6 +33,8 @@ SYMBOLS = [
     ("gpu_codec_encode_bgr_dev", C.c_bool, [C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_longlong, C.c_int, C.c_int,
                                             C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p,
                                             C.c_void_p, C.c_void_p]),
+    ("gpu_codec_encode_batch_bgr_dev", C.c_bool, [C.c_int, C.c_void_p, C.c_int, C.c_longlong, C.c_int, C.c_int, C.c_longlong,
+                                                  C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p]),
     ("gpu_codec_encode_bgr_dev_noalloc", C.c_bool, [C.c_void_p, C.c_int, C.c_int, C.c_longlong, C.c_void_p, C.c_size_t,
                                                     C.c_void_p, C.c_void_p, C.c_void_p]),
     ("gpu_codec_decode_dev", C.c_bool, [C.c_int, C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_int,
@@ -200,6 +202,14 @@ def encode_dev(ctx: int, rows, width: int, height: int, row_stride: int, payload
                                         chunk_off.data_ptr() if chunk_off is not None else None,
                                         qcoef.data_ptr() if qcoef is not None else None, _stream_ptr(stream)),
            "gpu_codec_encode_bgr_dev")
+
+
+def encode_batch_dev(ctx: int, frames, n_frames: int, frame_stride: int, width: int, height: int, row_stride: int,
+                     payload, frame_off, stream=None) -> None:
+    """gpu_codec_encode_batch_bgr_dev: n_frames frames in one launch; frame_off is an int64[n_frames+1] tensor."""
+    _check(load().gpu_codec_encode_batch_bgr_dev(ctx, frames.data_ptr(), n_frames, frame_stride, width, height, row_stride,
+                                                 payload.data_ptr(), payload.numel(), frame_off.data_ptr(),
+                                                 _stream_ptr(stream)), "gpu_codec_encode_batch_bgr_dev")
 
 
 def encode_dev_noalloc(rows, width: int, height: int, row_stride: int, payload, payload_len, status, stream=None) -> None:

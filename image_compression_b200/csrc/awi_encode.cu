@@ -248,12 +248,15 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
     S.amb[tid] = 0;
     __syncthreads();
     const int tile = S.tile;
-    const int mb_first = P.mb0 + tile * TILE_MB;                 // global raster index
+    // batches: tiles_per_frame tiles per frame, frames frame_stride bytes apart, predictors restart per frame
+    const int frame = tile / P.tiles_per_frame, tile_in = tile - frame * P.tiles_per_frame;
+    const int mb_first = P.mb0 + tile_in * TILE_MB;              // raster index inside the frame
     const int n_mb = min(TILE_MB, P.mb1 - mb_first);
     const bool has_halo = mb_first > 0;
 
     // ---- A: stage pixels.  Thread = one 16-byte piece column (macroblock m, piece k) x 8 rows.
     {
+        const uint8_t* const rows = P.rows + (long long) frame * P.frame_stride;
         const int col = tid % (3 * TILE_MB), m = col / 3, k = col - 3 * m;
         const int r0 = tid / (3 * TILE_MB);                       // 0 or 1
         uint4 v[8];
@@ -265,12 +268,12 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
             const int xb = mx * 48 + k * 16;
             const int valid = P.width * 3 - xb;
             const int y0 = my * 16 + r0;
-            const uint8_t* src = P.rows + (long long) (P.height - 1 - y0) * P.stride + xb;
+            const uint8_t* src = rows + (long long) (P.height - 1 - y0) * P.stride + xb;
             if (P.align == 16 && valid >= 16 && y0 + 14 < P.height) {     // the common case: 8 plain 128-bit loads
 #pragma unroll
                 for (int i = 0; i < 8; i++) v[i] = __ldg(reinterpret_cast<const uint4*>(src - (long long) (2 * i) * P.stride));
             } else {
-#pragma unroll 1
+#pragma unroll
                 for (int i = 0; i < 8; i++)
                     if (y0 + 2 * i < P.height) v[i] = load_piece(src - (long long) (2 * i) * P.stride, valid, P.align);
             }
@@ -285,7 +288,7 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
                 const int my = g / P.mbw, mx = g - my * P.mbw;
                 const int xb = mx * 48 + kk * 16, y = my * 16 + row;
                 if (y < P.height)
-                    h = load_piece(P.rows + (long long) (P.height - 1 - y) * P.stride + xb, P.width * 3 - xb, P.align);
+                    h = load_piece(rows + (long long) (P.height - 1 - y) * P.stride + xb, P.width * 3 - xb, P.align);
             }
             reinterpret_cast<uint4*>(S.halo)[tid] = h;
         }
@@ -479,7 +482,7 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
     // optional per-chunk outputs (tests, decode side-info) need the coefficient buffer: before it is reused
     if (P.qcoef != nullptr) {
         if (my_mb < n_mb) {
-            uint32_t* dst = reinterpret_cast<uint32_t*>(P.qcoef + ((long long) (mb_first - P.mb0) * 6 + tid) * 64);
+            uint32_t* dst = reinterpret_cast<uint32_t*>(P.qcoef + ((long long) (tile / P.tiles_per_frame) * (P.mb1 - P.mb0) * 6 + (long long) (mb_first - P.mb0) * 6 + tid) * 64);
 #pragma unroll
             for (int i = 0; i < 16; i++) dst[i] = S.coef[coef_word(tid, i)];
         }
@@ -508,7 +511,7 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
         const unsigned long long at = S.tile_base;
         const bool fits = at + ((total + 15u) >> 4) <= P.stage_cap_units;
         if (P.chunk_off != nullptr && my_mb < n_mb)
-            P.chunk_off[(long long) (mb_first - P.mb0) * 6 + tid] = my_off;          // tile-relative; the gather pass adds the tile's offset
+            P.chunk_off[(long long) (tile / P.tiles_per_frame) * (P.mb1 - P.mb0) * 6 + (long long) (mb_first - P.mb0) * 6 + tid] = my_off;          // tile-relative; the gather pass adds the tile's offset
         if (fits) {
             uint8_t* out = P.stage + at * 16;
             if (compact_ok) {
@@ -562,7 +565,7 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
         if (lane == 0) {
             st_desc(P.desc + tile, FLAG_PFX | (excl + total));
             S.tile_base = excl;
-            if (mb_first + n_mb >= P.mb1) *P.out_len = excl + total;      // last tile: payload length
+            if (tile == P.n_tiles - 1) *P.out_len = excl + total;         // last tile: payload length
         }
     }
     // meanwhile / afterwards: every thread moves its own chunk to its place in the compacted tile
@@ -579,7 +582,7 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
         const bool fits = base + total <= P.out_cap;
         if (!fits && tid == 0) atomicOr(P.err, 1u);
         if (P.chunk_off != nullptr && my_mb < n_mb)
-            P.chunk_off[(long long) (mb_first - P.mb0) * 6 + tid] = (uint32_t) (base + my_off);
+            P.chunk_off[(long long) (tile / P.tiles_per_frame) * (P.mb1 - P.mb0) * 6 + (long long) (mb_first - P.mb0) * 6 + tid] = (uint32_t) (base + my_off);
         if (fits && compact_ok) {
             uint8_t* out = P.out + base;
             const uint32_t head = min(total, (uint32_t) ((4 - (reinterpret_cast<uintptr_t>(out) & 3)) & 3));
@@ -650,7 +653,8 @@ __global__ void __launch_bounds__(256) enc_gather_tiles(const uint8_t* __restric
                                                         const unsigned long long* __restrict__ tile_off, int n_tiles,
                                                         uint8_t* __restrict__ out, const unsigned long long* __restrict__ out_len,
                                                         unsigned long long out_cap, uint32_t* __restrict__ chunk_off,
-                                                        long long n_chunks) {
+                                                        int tiles_per_frame, int chunks_per_frame,
+                                                        unsigned long long* __restrict__ frame_off) {
     const int tile = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (tile >= n_tiles || *out_len > out_cap) return;
     const uint2 info = tile_info[tile];
@@ -667,9 +671,15 @@ __global__ void __launch_bounds__(256) enc_gather_tiles(const uint8_t* __restric
     for (uint32_t j = lane; j < n_words; j += 32) dw[j] = __funnelshift_r(sw[j], sw[j + 1], sh);
     const uint32_t tail0 = head + (n_words << 2);
     if (tail0 + lane < total) dst[tail0 + lane] = src[tail0 + lane];
+    const int frame = tile / tiles_per_frame, tile_in = tile - frame * tiles_per_frame;
+    if (frame_off != nullptr && lane == 0) {
+        if (tile_in == 0) frame_off[frame] = off;                              // where each frame's payload starts
+        if (tile == n_tiles - 1) frame_off[frame + 1] = off + total;           // ... and where the last one ends
+    }
     if (chunk_off != nullptr) {
-        const long long c0 = (long long) tile * (TILE_MB * 6);
-        for (int i = lane; i < TILE_MB * 6 && c0 + i < n_chunks; i += 32) chunk_off[c0 + i] += (uint32_t) off;
+        const int c_in = tile_in * (TILE_MB * 6);
+        const long long c0 = (long long) frame * chunks_per_frame + c_in;
+        for (int i = lane; i < TILE_MB * 6 && c_in + i < chunks_per_frame; i += 32) chunk_off[c0 + i] += (uint32_t) off;
     }
 }
 
@@ -689,12 +699,15 @@ cudaError_t launch_encode(const EncParams& P, int n_tiles, cudaStream_t stream) 
         if (e != cudaSuccess) return e;
         attr_set[dev] = true;
     }
-    awi_encode_kernel<<<n_tiles, THREADS, sizeof(EncSmem), stream>>>(P);
+    EncParams Q = P;
+    Q.n_tiles = n_tiles;
+    if (Q.tiles_per_frame <= 0) { Q.tiles_per_frame = n_tiles; Q.frame_stride = 0; }      // a single frame
+    awi_encode_kernel<<<n_tiles, THREADS, sizeof(EncSmem), stream>>>(Q);
     if (P.stage != nullptr) {
-        const long long n_chunks = (long long) (P.mb1 - P.mb0) * 6;
         enc_scan_tiles<<<1, 1024, 0, stream>>>(P.tile_info, n_tiles, P.tile_off, P.out_len, P.chain, P.out_cap, P.err);
         enc_gather_tiles<<<(n_tiles + 7) / 8, 256, 0, stream>>>(P.stage, P.tile_info, P.tile_off, n_tiles, P.out, P.out_len,
-                                                                 P.out_cap, P.chunk_off, n_chunks);
+                                                                 P.out_cap, P.chunk_off, Q.tiles_per_frame,
+                                                                 (P.mb1 - P.mb0) * 6, P.frame_off);
     }
     return cudaGetLastError();
 }

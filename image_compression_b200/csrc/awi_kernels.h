@@ -35,7 +35,10 @@ struct EncParams {
     int width, height;            // full image
     int align;                    // 16, 4 or 1: guaranteed alignment of rows and stride
     int mbw;                      // macroblocks per row
-    int mb0, mb1;                 // raster macroblock range [mb0, mb1) to encode
+    int mb0, mb1;                 // raster macroblock range [mb0, mb1) to encode (of every frame of a batch)
+    int tiles_per_frame;          // batches: tiles per frame (0 = single frame); the grid covers frames x tiles
+    long long frame_stride;       // batches: bytes between consecutive frames' pixel arrays
+    unsigned long long* frame_off;  // batches, optional: n_frames+1 payload offsets (two-pass mode)
     int sm_count;                 // filled by launch_encode
     int n_tiles;                  // filled by launch_encode: tiles of ENC_TILE_MB macroblocks covering the range
     uint8_t* out;                 // payload bytes for this range

@@ -206,7 +206,8 @@ __global__ void colour_kernel(const uint8_t* in, size_t n, int inverse, uint8_t*
 
 bool encode_dev_impl(Ctx* c, const uint8_t* d_rows, int width, int height, long long stride, int wy0, int wy1,
                      int r0, int r1, uint8_t* d_payload, size_t cap, uint64_t* d_len, uint32_t* d_chunk_off,
-                     int8_t* d_qcoef, cudaStream_t st, unsigned long long* d_chain = nullptr) {
+                     int8_t* d_qcoef, cudaStream_t st, unsigned long long* d_chain = nullptr, int n_frames = 1,
+                     long long frame_stride = 0, unsigned long long* d_frame_off = nullptr) {
     if (width <= 0 || height <= 0) return fail("encode: bad geometry %dx%d", width, height);
     if (stride < 3ll * width) return fail("encode: row_stride %lld < 3*width", stride);
     const int mbw = (width + 15) / 16, mbh = (height + 15) / 16;
@@ -218,7 +219,9 @@ bool encode_dev_impl(Ctx* c, const uint8_t* d_rows, int width, int height, long 
     if (!d_rows || !d_payload) return fail("encode: null device pointer");
 
     const long long n_mb = (long long) (r1 - r0) * mbw;
-    const int n_tiles = (int) ((n_mb + awi::ENC_TILE_MB - 1) / awi::ENC_TILE_MB);
+    const int tiles_per_frame = (int) ((n_mb + awi::ENC_TILE_MB - 1) / awi::ENC_TILE_MB);
+    if (n_frames < 1 || (long long) tiles_per_frame * n_frames > (1ll << 30)) return fail("encode: bad frame count %d", n_frames);
+    const int n_tiles = tiles_per_frame * n_frames;
     CU(cudaSetDevice(c->dev));
     // two-pass encode: tiles go to a staging buffer in completion order (no tile ever waits for
     // another), then a scan + gather place them; scratch = header + (where,bytes) + offset per tile
@@ -248,6 +251,9 @@ bool encode_dev_impl(Ctx* c, const uint8_t* d_rows, int width, int height, long 
     P.tile_info = reinterpret_cast<uint2*>(c->enc_ws.p + ENC_WS_HEADER);
     P.tile_off = reinterpret_cast<unsigned long long*>(c->enc_ws.p + ENC_WS_HEADER + (size_t) n_tiles * 8);
     P.chain = d_chain;
+    P.tiles_per_frame = tiles_per_frame;
+    P.frame_stride = frame_stride;
+    P.frame_off = d_frame_off;
     P.err = c->d_err;
     P.chunk_off = d_chunk_off;
     P.qcoef = d_qcoef;
@@ -393,6 +399,19 @@ bool gpu_codec_encode_bgr_dev(int ctx, const uint8_t* d_rows, int width, int hei
                            payload_cap, d_payload_len, d_chunk_off, d_qcoef, st);
 }
 
+bool gpu_codec_encode_batch_bgr_dev(int ctx, const uint8_t* d_frames, int n_frames, long long frame_stride, int width,
+                                    int height, long long row_stride, uint8_t* d_payload, size_t payload_cap,
+                                    uint64_t* d_frame_off, void* stream) {
+    Ctx* c = get_ctx(ctx);
+    if (!c) return false;
+    if (n_frames < 1 || frame_stride < row_stride * (long long) height) return fail("encode_batch: bad frame count or frame stride");
+    if (!d_frame_off) return fail("encode_batch: null device pointer");
+    const int mbh = (height + 15) / 16;
+    return encode_dev_impl(c, d_frames, width, height, row_stride, 0, height, 0, mbh, d_payload, payload_cap, nullptr, nullptr,
+                           nullptr, (cudaStream_t) stream, nullptr, n_frames, frame_stride,
+                           reinterpret_cast<unsigned long long*>(d_frame_off));
+}
+
 bool gpu_codec_decode_dev(int ctx, const uint8_t* d_payload, size_t len, int width, int height, int mb_row0,
                           int mb_row1, uint8_t* d_dst, long long row_stride, int rgb_topdown,
                           const uint32_t* d_chunk_off, void* stream) {
@@ -516,6 +535,60 @@ bool gpu_codec_encode_bgr(const uint8_t* bmp_rows, int width, int height, int ro
     return true;
 }
 
+// One device's share of a host batch: frames i = first, first+step, ...  They are copied in groups of
+// ~SUB_BYTES on the copy stream; each group is encoded by ONE set of launches (batch kernel) as soon as it
+// has landed; payloads accumulate in c->out with their offsets in d_off.
+static bool encode_batch_on_ctx(Ctx* c, const uint8_t* const* frames, int n_frames, int first, int step, int width, int height,
+                                int row_stride, uint8_t** payloads, size_t* payload_lens) {
+    const int mbw = (width + 15) / 16, mbh = (height + 15) / 16;
+    const int n_mine = first < n_frames ? (n_frames - first + step - 1) / step : 0;
+    if (n_mine == 0) return true;
+    const size_t frame_bytes = (size_t) height * row_stride;
+    const size_t fs = (frame_bytes + 255) / 256 * 256;                 // device frame stride
+    const size_t cap = (size_t) n_mine * ((size_t) mbw * mbh * 6 * 121) + 16;
+    CU(cudaSetDevice(c->dev));
+    if (!ensure(c->in, fs * n_mine) || !ensure(c->out, cap)) return false;
+    unsigned long long* d_off = nullptr;                               // n_mine + 1 offsets, device + pinned host copy
+    CU(cudaMalloc(&d_off, (size_t) (n_mine + 1) * 8));
+    unsigned long long* h_off = static_cast<unsigned long long*>(pool_get((size_t) (n_mine + 1) * 8));
+    bool ok = h_off != nullptr;
+    if (!ok) fail("encode_batch: out of page-locked host memory");
+    int per_group = (int) (SUB_BYTES / fs);
+    if (per_group < 1) per_group = 1;
+    auto body = [&]() -> bool {
+        CU(cudaMemsetAsync(c->d_run, 0, 8, c->stream));
+        int gi = 0;
+        for (int f0 = 0; f0 < n_mine; f0 += per_group, gi++) {
+            const int f1 = f0 + per_group < n_mine ? f0 + per_group : n_mine;
+            for (int f = f0; f < f1; f++)
+                CU(cudaMemcpyAsync(c->in.p + (size_t) f * fs, frames[first + (size_t) f * step], frame_bytes, cudaMemcpyHostToDevice,
+                                   c->copy_stream));
+            cudaEvent_t ev = c->ev[gi % MAX_SUB];
+            CU(cudaEventRecord(ev, c->copy_stream));
+            CU(cudaStreamWaitEvent(c->stream, ev, 0));
+            if (!encode_dev_impl(c, c->in.p + (size_t) f0 * fs, width, height, row_stride, 0, height, 0, mbh, c->out.p, cap, nullptr,
+                                 nullptr, nullptr, c->stream, c->d_run, f1 - f0, (long long) fs, d_off + f0))
+                return false;
+        }
+        CU(cudaMemcpyAsync(h_off, d_off, (size_t) (n_mine + 1) * 8, cudaMemcpyDeviceToHost, c->stream));
+        if (!check_err(c, c->stream, "encode_batch")) return false;
+        for (int f = 0; f < n_mine; f++) {
+            const size_t n = (size_t) (h_off[f + 1] - h_off[f]);
+            const int i = first + f * step;
+            payloads[i] = static_cast<uint8_t*>(pool_get(n));
+            if (!payloads[i]) return fail("encode_batch: out of page-locked host memory");
+            payload_lens[i] = n;
+            CU(cudaMemcpyAsync(payloads[i], c->out.p + h_off[f], n, cudaMemcpyDeviceToHost, c->stream));
+        }
+        CU(cudaStreamSynchronize(c->stream));
+        return true;
+    };
+    ok = ok && body();
+    if (h_off) pool_put(h_off);
+    cudaFree(d_off);
+    return ok;
+}
+
 bool gpu_codec_encode_batch_bgr(const uint8_t* const* frames, int n_frames, int width, int height, int row_stride,
                                 uint8_t** payloads, size_t* payload_lens) {
     if (g_ctx.empty()) return fail("encode_batch: not initialised (call gpu_codec_init)");
@@ -523,30 +596,19 @@ bool gpu_codec_encode_batch_bgr(const uint8_t* const* frames, int n_frames, int 
         return fail("encode_batch: bad arguments");
     for (int i = 0; i < n_frames; i++) { payloads[i] = nullptr; payload_lens[i] = 0; }
     const int G = (int) g_ctx.size();
-    const int mbh = (height + 15) / 16;
     std::vector<std::string> errs(G);
-    std::vector<std::thread> workers;
-    for (int g = 0; g < G; g++) {
-        workers.emplace_back([&, g]() {
-            Ctx* c = g_ctx[g];
-            std::lock_guard<std::mutex> lk(c->mu);
-            auto body = [&]() -> bool {
-                for (int i = g; i < n_frames; i += G) {
-                    if (!encode_stripe_async(c, frames[i], width, height, row_stride, 0, mbh)) return false;
-                    if (!check_err(c, c->stream, "encode_batch")) return false;
-                    const size_t n = (size_t) *c->h_len;
-                    payloads[i] = static_cast<uint8_t*>(pool_get(n));
-                    if (!payloads[i]) return fail("encode_batch: out of page-locked host memory");
-                    payload_lens[i] = n;
-                    CU(cudaMemcpyAsync(payloads[i], c->out.p, n, cudaMemcpyDeviceToHost, c->stream));
-                    CU(cudaStreamSynchronize(c->stream));
-                }
-                return true;
-            };
-            if (!body()) errs[g] = g_last_error;
-        });
+    auto run = [&](int g) {
+        Ctx* c = g_ctx[g];
+        std::lock_guard<std::mutex> lk(c->mu);
+        if (!encode_batch_on_ctx(c, frames, n_frames, g, G, width, height, row_stride, payloads, payload_lens)) errs[g] = g_last_error;
+    };
+    if (G == 1) {
+        run(0);
+    } else {
+        std::vector<std::thread> workers;
+        for (int g = 0; g < G; g++) workers.emplace_back(run, g);
+        for (auto& t : workers) t.join();
     }
-    for (auto& t : workers) t.join();
     for (int g = 0; g < G; g++)
         if (!errs[g].empty()) {
             for (int i = 0; i < n_frames; i++) { gpu_codec_free(payloads[i]); payloads[i] = nullptr; payload_lens[i] = 0; }

@@ -116,6 +116,14 @@ bool gpu_codec_encode_bgr_dev(int ctx, const uint8_t* d_rows, int width, int hei
                               uint8_t* d_payload, size_t payload_cap, uint64_t* d_payload_len,
                               uint32_t* d_chunk_off, int8_t* d_qcoef, void* stream);
 
+/* Image-parallel batch on one device: n_frames equally sized frames, frame_stride bytes apart, each
+ * encoded as its own stream (DC predictors restart per frame, awi.c:91-92) by ONE set of kernel
+ * launches.  The payloads are concatenated in d_payload in frame order; d_frame_off receives
+ * n_frames+1 offsets (frame i occupies [off[i], off[i+1])). */
+bool gpu_codec_encode_batch_bgr_dev(int ctx, const uint8_t* d_frames, int n_frames, long long frame_stride,
+                                    int width, int height, long long row_stride,
+                                    uint8_t* d_payload, size_t payload_cap, uint64_t* d_frame_off, void* stream);
+
 /* Whole-frame encode of device-resident rows that allocates nothing (no counterpart in
  * the reference; it exists for callers of this library that must not allocate device
  * memory while encoding: engines that own all device memory through their own pool,

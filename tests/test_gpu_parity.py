@@ -201,3 +201,23 @@ def test_sample1_if_present(gpu, golden):
     sink = bmp.RGBPixelOutput()
     assert awi.decompress_awi(awi.AWIFileInput(io.BytesIO(out.getvalue())), sink)
     assert sink.pixels.shape == (427, 640, 3)
+
+
+def test_batch_dev_one_launch(gpu, port):
+    """gpu_codec_encode_batch_bgr_dev: frames in one launch, predictors restart per frame."""
+    import torch
+    for w, h, n in ((192, 108, 7), (528, 48, 3), (37, 21, 5)):
+        stride = synth.bmp_stride(w)
+        frames = [synth.frame_bgr_bottomup("photo" if f % 2 else "noise", w, h, 0xA11CE04, f).reshape(-1) for f in range(n)]
+        fs = ((stride * h + 255) // 256) * 256
+        buf = torch.zeros(n * fs, dtype=torch.uint8, device="cuda")
+        for f in range(n):
+            buf[f * fs: f * fs + stride * h] = torch.from_numpy(frames[f]).cuda()
+        payload = torch.empty(n * (gpu.max_payload_bytes(w, h) + 16), dtype=torch.uint8, device="cuda")
+        off = torch.zeros(n + 1, dtype=torch.int64, device="cuda")
+        gpu.encode_batch_dev(0, buf, n, fs, w, h, stride, payload, off)
+        gpu.sync_check(0)
+        o = off.cpu().numpy()
+        for f in range(n):
+            want = port.encode_bgr(frames[f], w, h, stride)
+            assert payload[o[f]:o[f + 1]].cpu().numpy().tobytes() == want.tobytes(), (w, h, f)
