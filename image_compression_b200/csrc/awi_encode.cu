@@ -607,7 +607,8 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
 }
 
 // ---------------------------------------------------------------- two-pass mode, passes 2 and 3
-// Exclusive scan of the tiles' byte counts in tile order (one CTA; a few ten thousand tiles).
+// Exclusive scan of the tiles' byte counts in tile order (one CTA of 32 warps; each warp owns a
+// contiguous range and reads it 32 tiles at a time, coalesced).
 __global__ void __launch_bounds__(1024) enc_scan_tiles(const uint2* __restrict__ tile_info, int n_tiles,
                                                        unsigned long long* __restrict__ tile_off,
                                                        unsigned long long* __restrict__ out_len,
@@ -615,17 +616,13 @@ __global__ void __launch_bounds__(1024) enc_scan_tiles(const uint2* __restrict__
                                                        unsigned long long out_cap, unsigned int* err) {
     __shared__ unsigned long long wsum[32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int per = (n_tiles + 1023) / 1024;
-    const int t0 = min(n_tiles, tid * per), t1 = min(n_tiles, t0 + per);
+    const int per = ((n_tiles + 31) / 32 + 31) & ~31;               // tiles per warp, a multiple of 32
+    const int t0 = min(n_tiles, warp * per), t1 = min(n_tiles, t0 + per);
     unsigned long long mine = 0;
-    for (int t = t0; t < t1; t++) mine += tile_info[t].y;
-    unsigned long long incl = mine;
+    for (int t = t0 + lane; t < t1; t += 32) mine += tile_info[t].y;
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        unsigned long long v = __shfl_up_sync(0xffffffffu, incl, o);
-        if (lane >= o) incl += v;
-    }
-    if (lane == 31) wsum[warp] = incl;
+    for (int o = 16; o > 0; o >>= 1) mine += __shfl_xor_sync(0xffffffffu, mine, o);
+    if (lane == 0) wsum[warp] = mine;
     __syncthreads();
     if (warp == 0) {
         unsigned long long w = wsum[lane], wi = w;
@@ -644,8 +641,19 @@ __global__ void __launch_bounds__(1024) enc_scan_tiles(const uint2* __restrict__
         }
     }
     __syncthreads();
-    unsigned long long run = wsum[warp] + incl - mine;
-    for (int t = t0; t < t1; t++) { tile_off[t] = run; run += tile_info[t].y; }
+    unsigned long long run = wsum[warp];
+    for (int i0 = t0; i0 < t1; i0 += 32) {
+        const int t = i0 + lane;
+        const unsigned long long v = t < t1 ? (unsigned long long) tile_info[t].y : 0ull;
+        unsigned long long incl = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            unsigned long long u = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += u;
+        }
+        if (t < t1) tile_off[t] = run + incl - v;
+        run += __shfl_sync(0xffffffffu, incl, 31);
+    }
 }
 
 // One warp per tile: staging (16-byte aligned, completion order) -> payload (byte offsets, tile order).
