@@ -60,10 +60,17 @@ __global__ void __launch_bounds__(256) dec_scan_segments(const uint8_t* __restri
                                                          uint8_t* __restrict__ Lg, unsigned long long* __restrict__ table) {
     __shared__ __align__(16) uint8_t s[SEG_STAGE];
     __shared__ uint8_t L[SEG];
+    __shared__ unsigned jump[SEG];
     const unsigned long long seg_start = (unsigned long long) blockIdx.x * SEG;
-    for (int i = threadIdx.x; i < SEG_STAGE; i += 256) {
-        unsigned long long g = seg_start + i;
-        s[i] = g < P ? payload[g] : 0;
+    if ((reinterpret_cast<uintptr_t>(payload) & 15) == 0 && seg_start + SEG_STAGE <= P) {      // whole stage inside the payload
+        static_assert(SEG_STAGE % 16 == 0, "stage is copied in 16-byte pieces");
+        const uint4* src = reinterpret_cast<const uint4*>(payload + seg_start);
+        for (int i = threadIdx.x; i < SEG_STAGE / 16; i += 256) reinterpret_cast<uint4*>(s)[i] = __ldg(src + i);
+    } else {
+        for (int i = threadIdx.x; i < SEG_STAGE; i += 256) {
+            unsigned long long g = seg_start + i;
+            s[i] = g < P ? payload[g] : 0;
+        }
     }
     __syncthreads();
     for (int p = threadIdx.x; p < SEG; p += 256) {
@@ -77,24 +84,45 @@ __global__ void __launch_bounds__(256) dec_scan_segments(const uint8_t* __restri
         if (g < P) Lg[g] = (uint8_t) len;
     }
     __syncthreads();
-    if (threadIdx.x < MAXCH) {
-        int pos = threadIdx.x;
-        unsigned long long cnt = 0;
-        bool ok = true;
-        const long long remain = (long long) (P - seg_start);       // bytes of payload from seg_start on
-        const int lim = remain < SEG ? (int) remain : SEG;
-        if (pos > lim) ok = false;
-        while (ok && pos < lim) {
-            int l = L[pos];
-            if (l == 0) { ok = false; break; }
-            pos += l;
-            cnt++;
+    // entry offset -> (exit offset into the next segment, chunks passed) for each of the 184 possible entry
+    // offsets, by pointer jumping over jump[p] = (where the chain from p has got to, chunks counted), one
+    // 32-bit word per position so a pair is always read consistently; 10 doublings cover the longest
+    // chain (2048/3 chunks).  In-place updates may see a neighbour's old or new word: both are valid jumps.
+    const long long remain = (long long) (P - seg_start);           // bytes of payload from seg_start on
+    const int lim = remain < SEG ? (int) remain : SEG;              // in the last segment a legal chain ends exactly at lim
+    constexpr unsigned DEAD = 0xffffu;
+    for (int p = threadIdx.x; p < SEG; p += 256) {
+        unsigned w = DEAD;
+        const int l = L[p];
+        if (l != 0 && p < lim) {
+            const int q = p + l;                                     // q <= lim in the last segment (longer chunks were zeroed)
+            w = (q < lim ? (unsigned) q : (unsigned) (SEG + (q - lim))) | (1u << 16);
         }
-        // in the last segment a legal chain ends exactly at the payload end
-        if (ok && remain <= SEG && pos != lim) ok = false;
-        int exit = pos - SEG;
-        if (remain <= SEG) exit = 0;
-        table[(unsigned long long) blockIdx.x * MAXCH + threadIdx.x] = ok ? ent_make(cnt, exit) : 0ull;
+        jump[p] = w;
+    }
+    __syncthreads();
+    for (int round = 0; round < 10; round++) {
+        int moved = 0;
+        for (int p = threadIdx.x; p < SEG; p += 256) {
+            const unsigned w = jump[p], n = w & 0xffffu;
+            if (n < (unsigned) SEG) {
+                const unsigned w2 = jump[n], n2 = w2 & 0xffffu;
+                jump[p] = n2 == DEAD ? DEAD : (n2 | ((w >> 16) + (w2 >> 16)) << 16);
+                moved = 1;
+            }
+        }
+        if (!__syncthreads_or(moved)) break;                         // every chain has left the segment (or died)
+    }
+    if (threadIdx.x < MAXCH) {
+        const int e = threadIdx.x;
+        unsigned long long r = 0ull;
+        if (e == lim) {
+            r = ent_make(0, 0);                                      // entering exactly at the payload end: nothing left
+        } else if (e < lim) {
+            const unsigned w = jump[e], n = w & 0xffffu;
+            if (n != DEAD && n >= (unsigned) SEG) r = ent_make(w >> 16, remain <= SEG ? 0 : (int) (n - SEG));
+        }
+        table[(unsigned long long) blockIdx.x * MAXCH + threadIdx.x] = r;
     }
 }
 
