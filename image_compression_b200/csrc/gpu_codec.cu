@@ -217,6 +217,7 @@ bool encode_dev_impl(Ctx* c, const uint8_t* d_rows, int width, int height, long 
     if (wy0 > need_lo || wy1 < need_hi || wy1 > height || wy0 < 0)
         return fail("encode: pixel window [%d,%d) does not cover rows [%d,%d)", wy0, wy1, need_lo, need_hi);
     if (!d_rows || !d_payload) return fail("encode: null device pointer");
+    if (d_chunk_off && cap >= (1ull << 32)) return fail("encode: chunk offsets are 32-bit; payload_cap must stay below 4 GiB when they are requested");
 
     const long long n_mb = (long long) (r1 - r0) * mbw;
     const int tiles_per_frame = (int) ((n_mb + awi::ENC_TILE_MB - 1) / awi::ENC_TILE_MB);
