@@ -30,7 +30,11 @@ constexpr int SEG_STAGE = SEG + 208; // segment + longest chunk + read-ahead
 constexpr int FAN = 32;              // children per node of the composition tree
 constexpr int DCT_MB = 256;          // macroblocks per DC-scan tile
 constexpr int REC_MB = 8;            // macroblocks per reconstruct CTA
-constexpr int REC_THREADS = REC_MB * 48;
+#ifndef REC_ROWS
+#define REC_ROWS 2                       // image rows per IDCT thread (8/REC_ROWS threads per block)
+#endif
+constexpr int REC_TPB = 8 / REC_ROWS;     // IDCT threads per 8x8 block
+constexpr int REC_THREADS = REC_MB * 6 * REC_TPB;
 
 // map entry: bit 63 valid | bits 8..47 chunk count | bits 0..7 exit offset into the next node
 constexpr unsigned long long ENT_OK = 1ull << 63;
@@ -380,14 +384,16 @@ __global__ void __launch_bounds__(REC_THREADS) dec_reconstruct(DecParams P, cons
     }
     __syncthreads();
 
-    // ---- IDCT: 8 threads per block, one output row each.  dct.c:64-78: for u, for v:
+    // ---- IDCT: REC_TPB threads per block, REC_ROWS output rows each.  dct.c:64-78: for u, for v:
     //      sum += (((cu*cv)*coef)*cos[y][u])*cos[x][v], all fp64, strictly in that order.
     {
-        const int blk = tid >> 3, y = tid & 7;
+        const int blk = tid / REC_TPB, y0 = (tid % REC_TPB) * REC_ROWS;
         if (blk < n_ch) {
-            double sum[8];
+            double sum[REC_ROWS][8];
 #pragma unroll
-            for (int x = 0; x < 8; x++) sum[x] = 0.0;
+            for (int r = 0; r < REC_ROWS; r++)
+#pragma unroll
+                for (int x = 0; x < 8; x++) sum[r][x] = 0.0;
             unsigned long long m = S.mask[blk];
             const int* cf = S.coef[blk];
             while (m) {
@@ -395,27 +401,36 @@ __global__ void __launch_bounds__(REC_THREADS) dec_reconstruct(DecParams P, cons
                 m &= m - 1;
                 const int u = k >> 3, v = k & 7;
                 const double a = __dmul_rn(S.cucv[k], (double) cf[k]);
-                const double b = __dmul_rn(a, S.cost[u * 8 + y]);                             // cos_table[y][u]
+                double b[REC_ROWS];
+#pragma unroll
+                for (int r = 0; r < REC_ROWS; r++) b[r] = __dmul_rn(a, S.cost[u * 8 + y0 + r]);        // cos_table[y][u]
                 const double2* cx = reinterpret_cast<const double2*>(&S.cost[v * 8]);          // cos_table[x][v], x = 0..7
 #pragma unroll
                 for (int x2 = 0; x2 < 4; x2++) {
                     const double2 c = cx[x2];
-                    sum[2 * x2] = __dadd_rn(sum[2 * x2], __dmul_rn(b, c.x));
-                    sum[2 * x2 + 1] = __dadd_rn(sum[2 * x2 + 1], __dmul_rn(b, c.y));
+#pragma unroll
+                    for (int r = 0; r < REC_ROWS; r++) {
+                        sum[r][2 * x2] = __dadd_rn(sum[r][2 * x2], __dmul_rn(b[r], c.x));
+                        sum[r][2 * x2 + 1] = __dadd_rn(sum[r][2 * x2 + 1], __dmul_rn(b[r], c.y));
+                    }
                 }
             }
             const int mb = blk / 6, type = blk - 6 * mb;
-            uint32_t px[8];
 #pragma unroll
-            for (int x = 0; x < 8; x++) px[x] = (uint32_t) clamp_trunc(__dadd_rn(__dmul_rn(0.25, sum[x]), 128.0));
-            uint8_t* dstp;
-            if (type < 4) dstp = &S.yp[((type >> 1) << 3) + y][mb * 16 + ((type & 1) << 3)];
-            else if (type == 4) dstp = &S.cbp[y][mb * 8];
-            else dstp = &S.crp[y][mb * 8];
-            uint2 w;
-            w.x = px[0] | (px[1] << 8) | (px[2] << 16) | (px[3] << 24);
-            w.y = px[4] | (px[5] << 8) | (px[6] << 16) | (px[7] << 24);
-            *reinterpret_cast<uint2*>(dstp) = w;
+            for (int r = 0; r < REC_ROWS; r++) {
+                const int y = y0 + r;
+                uint32_t px[8];
+#pragma unroll
+                for (int x = 0; x < 8; x++) px[x] = (uint32_t) clamp_trunc(__dadd_rn(__dmul_rn(0.25, sum[r][x]), 128.0));
+                uint8_t* dstp;
+                if (type < 4) dstp = &S.yp[((type >> 1) << 3) + y][mb * 16 + ((type & 1) << 3)];
+                else if (type == 4) dstp = &S.cbp[y][mb * 8];
+                else dstp = &S.crp[y][mb * 8];
+                uint2 w;
+                w.x = px[0] | (px[1] << 8) | (px[2] << 16) | (px[3] << 24);
+                w.y = px[4] | (px[5] << 8) | (px[6] << 16) | (px[7] << 24);
+                *reinterpret_cast<uint2*>(dstp) = w;
+            }
         }
     }
     __syncthreads();
