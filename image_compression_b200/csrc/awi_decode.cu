@@ -29,7 +29,10 @@ constexpr int MAXCH = 184;           // longest legal chunk: 12 + 63*(8+15) + 8 
 constexpr int SEG_STAGE = SEG + 208; // segment + longest chunk + read-ahead
 constexpr int FAN = 32;              // children per node of the composition tree
 constexpr int DCT_MB = 256;          // macroblocks per DC-scan tile
-constexpr int REC_MB = 8;            // macroblocks per reconstruct CTA
+#ifndef REC_MB_N
+#define REC_MB_N 8
+#endif
+constexpr int REC_MB = REC_MB_N;     // macroblocks per reconstruct CTA
 #ifndef REC_ROWS
 #define REC_ROWS 2                       // image rows per IDCT thread (8/REC_ROWS threads per block)
 #endif
