@@ -134,40 +134,43 @@ __global__ void __launch_bounds__(256) dec_scan_segments(const uint8_t* __restri
 }
 
 // ---------------------------------------------------------------- 2: compose
+// out[i][e] = children c0..c1 of node i applied in turn to entry e.  On the way, pre[c][e] records the state
+// in front of child c (entry offset into it, chunks counted before it) so that the top-down pass needs one
+// look-up per child instead of a chain of them.
 __global__ void __launch_bounds__(192) dec_compose(const unsigned long long* __restrict__ in, long long n_in,
-                                                   unsigned long long* __restrict__ out) {
+                                                   unsigned long long* __restrict__ out,
+                                                   unsigned long long* __restrict__ pre) {
     if (threadIdx.x >= MAXCH) return;
     long long c0 = (long long) blockIdx.x * FAN, c1 = c0 + FAN < n_in ? c0 + FAN : n_in;
     int e = threadIdx.x;
     unsigned long long cnt = 0;
     bool ok = true;
     for (long long c = c0; c < c1; c++) {
-        unsigned long long t = in[c * MAXCH + e];
-        if (!(t & ENT_OK)) { ok = false; break; }
-        cnt += ent_cnt(t);
-        e = ent_exit(t);
+        pre[c * MAXCH + threadIdx.x] = ok ? ent_make(cnt, e) : 0ull;
+        if (ok) {
+            unsigned long long t = in[c * MAXCH + e];
+            if (!(t & ENT_OK)) ok = false;
+            else { cnt += ent_cnt(t); e = ent_exit(t); }
+        }
     }
     out[(long long) blockIdx.x * MAXCH + threadIdx.x] = ok ? ent_make(cnt, e) : 0ull;
 }
 
 // ---------------------------------------------------------------- 3: expand
-// node_in[i] = (entry offset, first chunk index) of parent i; fills the same for its children
+// state[i] = (entry offset, first chunk index) of node i; one thread per child, no chains.
 struct NodeState { unsigned long long first_chunk; int entry; int ok; };
 
-__global__ void dec_expand(const unsigned long long* __restrict__ child_table, long long n_child,
-                           const NodeState* __restrict__ parent, long long n_parent, NodeState* __restrict__ child) {
-    long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n_parent) return;
-    NodeState st = parent[i];
-    long long c0 = i * FAN, c1 = c0 + FAN < n_child ? c0 + FAN : n_child;
-    for (long long c = c0; c < c1; c++) {
-        child[c] = st;
-        if (st.ok) {
-            unsigned long long t = child_table[c * MAXCH + st.entry];
-            if (t & ENT_OK) { st.first_chunk += ent_cnt(t); st.entry = ent_exit(t); }
-            else st.ok = 0;
-        }
+__global__ void dec_expand(const unsigned long long* __restrict__ pre, long long n_child,
+                           const NodeState* __restrict__ parent, NodeState* __restrict__ child) {
+    long long c = (long long) blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= n_child) return;
+    NodeState st = parent[c / FAN];
+    if (st.ok) {
+        const unsigned long long p = pre[c * MAXCH + st.entry];
+        if (p & ENT_OK) { st.first_chunk += ent_cnt(p); st.entry = ent_exit(p); }
+        else st.ok = 0;
     }
+    child[c] = st;
 }
 
 __global__ void dec_root(const unsigned long long* __restrict__ top_table, NodeState* __restrict__ root,
@@ -489,7 +492,7 @@ struct DecLayout {
     long long n_seg;
     int levels;                       // tables[0] = segments ... tables[levels-1] has one node
     long long n_node[16];
-    size_t off_table[16], off_state[16];
+    size_t off_table[16], off_state[16], off_pre[16];   // off_pre[lv]: states in front of the children (level lv-1 nodes) of level lv
     size_t off_L, off_chunk_off, off_dcabs, off_tile_sum, off_tile_base, total;
     long long n_dct;
 };
@@ -505,6 +508,7 @@ static DecLayout dec_layout(unsigned long long P, long long n_chunks) {
         Lo.n_node[lv] = n;
         Lo.off_table[lv] = off; off = align_up(off + (size_t) n * MAXCH * 8, 256);
         Lo.off_state[lv] = off; off = align_up(off + (size_t) n * sizeof(NodeState), 256);
+        Lo.off_pre[lv + 1] = off; off = align_up(off + (size_t) n * MAXCH * 8, 256);
         lv++;
         if (n == 1) break;
         n = (n + FAN - 1) / FAN;
@@ -544,13 +548,13 @@ cudaError_t launch_decode(const DecParams& P, void* workspace, size_t workspace_
         auto table = [&](int lv) { return reinterpret_cast<unsigned long long*>(ws + Lo.off_table[lv]); };
         auto state = [&](int lv) { return reinterpret_cast<NodeState*>(ws + Lo.off_state[lv]); };
         dec_scan_segments<<<(unsigned) Lo.n_seg, 256, 0, stream>>>(P.payload, P.payload_len, Lg, table(0));
+        auto pre = [&](int lv) { return reinterpret_cast<unsigned long long*>(ws + Lo.off_pre[lv]); };
         for (int lv = 1; lv < Lo.levels; lv++)
-            dec_compose<<<(unsigned) Lo.n_node[lv], 192, 0, stream>>>(table(lv - 1), Lo.n_node[lv - 1], table(lv));
+            dec_compose<<<(unsigned) Lo.n_node[lv], 192, 0, stream>>>(table(lv - 1), Lo.n_node[lv - 1], table(lv), pre(lv));
         dec_root<<<1, 32, 0, stream>>>(table(Lo.levels - 1), state(Lo.levels - 1), (unsigned long long) n_chunks, err);
         for (int lv = Lo.levels - 1; lv >= 1; lv--) {
-            long long np = Lo.n_node[lv];
-            dec_expand<<<(unsigned) ((np + 127) / 128), 128, 0, stream>>>(table(lv - 1), Lo.n_node[lv - 1], state(lv), np,
-                                                                       state(lv - 1));
+            const long long nc = Lo.n_node[lv - 1];
+            dec_expand<<<(unsigned) ((nc + 127) / 128), 128, 0, stream>>>(pre(lv), nc, state(lv), state(lv - 1));
         }
         dec_emit_offsets<<<(unsigned) Lo.n_seg, 64, 0, stream>>>(Lg, P.payload_len, state(0), chunk_off,
                                                                 (unsigned long long) n_chunks);
