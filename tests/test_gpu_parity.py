@@ -221,3 +221,29 @@ def test_batch_dev_one_launch(gpu, port):
         for f in range(n):
             want = port.encode_bgr(frames[f], w, h, stride)
             assert payload[o[f]:o[f + 1]].cpu().numpy().tobytes() == want.tobytes(), (w, h, f)
+
+
+def test_random_geometry_and_content(gpu, port):
+    """Seeded sweep over ragged sizes x content kinds x row strides: encode bytes, chunk offsets and both
+    decode sinks against the oracle (host API end to end)."""
+    rng = np.random.default_rng(20261106)
+    for trial in range(40):
+        w = int(rng.integers(1, 700))
+        h = int(rng.integers(1, 300))
+        kind = ("noise", "photo", "flat")[trial % 3]
+        stride = synth.bmp_stride(w) + int(rng.choice([0, 0, 4, 12, 52]))
+        rgb = synth.frame_rgb_topdown(kind, w, h, int(rng.integers(1 << 30)), trial)
+        if trial % 5 == 0:                       # extremes: saturated colours and hard edges
+            rgb = np.where(rgb > 128, 255, 0).astype(np.uint8)
+        rows = np.zeros((h, stride), np.uint8)
+        rows[:, :3 * w] = rgb[::-1, :, ::-1].reshape(h, 3 * w)
+        rows[:, 3 * w:] = 0xAB                   # padding bytes must be ignored
+        want = port.encode_bgr(rows, w, h, stride)
+        got = gpu.encode_bgr(rows, w, h, stride)
+        assert got == want.tobytes(), (trial, kind, w, h, stride)
+        out = np.full(stride * h, 0xCD, np.uint8)
+        gpu.decode_to_bgr(got, w, h, stride, out=out)
+        ref_px = port.decode(want, w, h, stride)[0].reshape(h, stride)
+        o = out.reshape(h, stride)
+        assert (o[:, :3 * w] == ref_px[:, :3 * w]).all(), (trial, kind, w, h, stride)
+        assert (o[:, 3 * w:] == 0xCD).all()     # row padding left untouched
