@@ -15,6 +15,11 @@
 #include <stddef.h>
 #include <stdint.h>
 
+#ifdef AWI_USE_REFERENCE_HEADERS
+/* inside the reference tree: its own declarations (awi.h pulls in bitrw.h, pixelrw.h, block.h) */
+#include "awi.h"
+#else
+
 typedef struct { uint8_t b[16][16]; } Block16_u8;
 typedef struct { Block16_u8 r, g, b; } RGBBlock16;
 
@@ -53,6 +58,8 @@ typedef struct { char title[8]; uint32_t width, height; } AWIHeader;
 /* Same names, arguments and error behaviour as awi.h:45-46. */
 bool compress_to_awi(PixelInput* pi, BitsOutput* bo);
 bool decompress_awi(BitsInput* bi, PixelOutput* po);
+
+#endif /* AWI_USE_REFERENCE_HEADERS */
 
 /* Bulk variants for sources/sinks that hold the whole frame (what bmp.c's contexts can
  * provide with one fread/fwrite): no per-macroblock callbacks. */

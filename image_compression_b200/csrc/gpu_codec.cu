@@ -53,7 +53,7 @@ struct Ctx {
     cudaStream_t stream = nullptr;            // compute (and small copies)
     cudaStream_t copy_stream = nullptr;       // bulk H2D / D2H overlapped with compute
     cudaEvent_t ev[MAX_SUB] = { nullptr };
-    Buf enc_ws, enc_stage, dec_ws, in, out;
+    Buf enc_ws, enc_stage, dec_ws, in, out, frame_off;
     unsigned int* d_err = nullptr;
     unsigned long long* d_run = nullptr;      // running payload offset of a frame encoded in sub-stripes
     uint64_t* h_len = nullptr;                // pinned
@@ -89,7 +89,7 @@ void destroy_ctx(Ctx* c) {
     if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
     for (cudaEvent_t e : c->ev) if (e) cudaEventDestroy(e);
     if (c->d_run) cudaFree(c->d_run);
-    for (Buf* b : { &c->enc_ws, &c->enc_stage, &c->dec_ws, &c->in, &c->out })
+    for (Buf* b : { &c->enc_ws, &c->enc_stage, &c->dec_ws, &c->in, &c->out, &c->frame_off })
         if (b->p) cudaFree(b->p);
     if (c->d_err) cudaFree(c->d_err);
     if (c->h_len) cudaFreeHost(c->h_len);
@@ -548,9 +548,8 @@ static bool encode_batch_on_ctx(Ctx* c, const uint8_t* const* frames, int n_fram
     const size_t fs = (frame_bytes + 255) / 256 * 256;                 // device frame stride
     const size_t cap = (size_t) n_mine * ((size_t) mbw * mbh * 6 * 121) + 16;
     CU(cudaSetDevice(c->dev));
-    if (!ensure(c->in, fs * n_mine) || !ensure(c->out, cap)) return false;
-    unsigned long long* d_off = nullptr;                               // n_mine + 1 offsets, device + pinned host copy
-    CU(cudaMalloc(&d_off, (size_t) (n_mine + 1) * 8));
+    if (!ensure(c->in, fs * n_mine) || !ensure(c->out, cap) || !ensure(c->frame_off, (size_t) (n_mine + 1) * 8)) return false;
+    unsigned long long* d_off = reinterpret_cast<unsigned long long*>(c->frame_off.p);   // n_mine + 1 offsets (+ pinned host copy)
     unsigned long long* h_off = static_cast<unsigned long long*>(pool_get((size_t) (n_mine + 1) * 8));
     bool ok = h_off != nullptr;
     if (!ok) fail("encode_batch: out of page-locked host memory");
@@ -586,7 +585,6 @@ static bool encode_batch_on_ctx(Ctx* c, const uint8_t* const* frames, int n_fram
     };
     ok = ok && body();
     if (h_off) pool_put(h_off);
-    cudaFree(d_off);
     return ok;
 }
 

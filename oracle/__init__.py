@@ -38,8 +38,11 @@ def build(force: bool = False) -> None:
     ref_so = os.path.join(_HERE, "_ref", "libawi_ref.so")
     need = force or not os.path.exists(so) or (
         os.path.getmtime(so) < os.path.getmtime(os.path.join(_HERE, "awi_oracle.c")))
-    if os.path.isdir("/root/reference/src") and not os.path.exists(ref_so):
-        need = True
+    if os.path.isdir("/root/reference/src"):
+        cli = os.path.join(_HERE, "_ref", "ref_gpu_cli")
+        gpulib = os.path.join(os.path.dirname(_HERE), "image_compression_b200", "libgpu_codec.so")
+        if not os.path.exists(ref_so) or (os.path.exists(gpulib) and not os.path.exists(cli)):
+            need = True
     if need:
         subprocess.run(["make", "-C", _HERE], check=True, stdout=subprocess.DEVNULL)
 

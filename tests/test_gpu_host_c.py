@@ -106,3 +106,28 @@ def test_compress_to_awi_through_plugin_vtables(host, port):
     rows = synth.rows_from_rgb_topdown(rgb)
     want = port.encode_bgr(rows, w, h, synth.bmp_stride(w))
     assert bytes(sink) == oracle.awi_header(w, h) + want.tobytes()
+
+
+def test_reference_bmp_code_linked_against_our_awi(port, tmp_path):
+    """oracle/_ref/ref_gpu_cli = the reference's OWN bmp.c / bitrw.c / utils.c and headers linked with
+    host/awi_gpu.c in place of the reference's awi.c (built where /root/reference exists; the binary
+    travels).  The reference's BMP reader drives our compress_to_awi block by block, our decompress_awi
+    drives the reference's BMP writer."""
+    cli = os.path.join(ROOT, "oracle", "_ref", "ref_gpu_cli")
+    if not os.path.exists(cli):
+        pytest.skip("oracle/_ref/ref_gpu_cli not built on this machine")
+    w, h = 332, 205                                  # 3w is a multiple of 4: the reference's row padding is indeterminate
+    rows = synth.frame_bgr_bottomup("photo", w, h, synth.SEED_BASE + 2)
+    bmp = tmp_path / "in.bmp"
+    # pixel array at offset 138 like the reference's own sample (bfOffBits is honoured, bmp.c:35)
+    body = oracle.bmp_wrap(rows, w, h)
+    import struct
+    bmp.write_bytes(body[:10] + struct.pack("<I", 138) + body[14:54] + b"\0" * 84 + body[54:])
+    r = subprocess.run([cli, "convert", str(bmp), str(tmp_path / "out.awi")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    want = port.encode_bgr(rows, w, h, synth.bmp_stride(w))
+    assert (tmp_path / "out.awi").read_bytes() == oracle.awi_header(w, h) + want.tobytes()
+    r = subprocess.run([cli, "revert", str(tmp_path / "out.awi"), str(tmp_path / "back.bmp")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    back = (tmp_path / "back.bmp").read_bytes()
+    assert back[54:] == port.decode(want, w, h)[0].tobytes()
