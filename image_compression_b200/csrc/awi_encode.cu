@@ -301,15 +301,17 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
         const bool chroma = warp >= 4;
         // per-lane quantiser constants for natural positions (u, v), u = 0..7, and where
         // their quantised values go in the chunk
-        float gk[8], gc[8], gt[8];
+        float gk[8], gc[8];
         int pos[8];                                               // scan positions of my 8 coefficients
 #pragma unroll
         for (int u = 0; u < 8; u++) {
             gk[u] = d_gk[chroma][8 * u + v];
             gc[u] = d_gc[chroma][8 * u + v];
-            gt[u] = d_gt[chroma][8 * u + v];
             pos[u] = unscan_rt(8 * u + v);
         }
+        // one ambiguity threshold for every position (the tightest of the table): a few more exact
+        // recomputations, but the per-coefficient test is a running maximum and 8 registers are saved
+        const float gt = chroma ? AWI_GT_MIN_CHROMA : AWI_GT_MIN_LUMA;
         float* tr = S.tr[warp];
         uint8_t* coefb = reinterpret_cast<uint8_t*>(S.coef);
         const int cBG = jb & 1 ? pack16(-813, -4187) : pack16(5000, -3313), cR = jb & 1 ? pack16(5000, 0) : pack16(-1687, 0);
@@ -348,16 +350,16 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
             for (int u = 0; u < 8; u++) d[u] = tr[jb * 72 + u * 9 + v];
             aan8(d[0], d[1], d[2], d[3], d[4], d[5], d[6], d[7]);                 // column pass: d[u] = coefficient (u, v)
 
-            uint32_t flags = 0;
             float t[8];
+            const float dist0 = quant_absdiff(d[0], gk[0], gc[0], t[0]);
+            float dist = v == 0 ? 0.0f : dist0;              // the DC (u = v = 0) is exact, never ambiguous
 #pragma unroll
-            for (int u = 0; u < 8; u++) flags |= quant_flag(d[u], gk[u], gc[u], gt[u], t[u]) ? (1u << u) : 0u;
+            for (int u = 1; u < 8; u++) dist = fmaxf(dist, quant_absdiff(d[u], gk[u], gc[u], t[u]));
             uint32_t q0 = __float_as_uint(t[0]);
             if (v == 0) {             // exact DC: d[0] is the integer sum of the 64 centred samples
                 const int cdc = dc_coef_from_sum((int) d[0]);
                 const int q = chroma ? quant_int(cdc, 17) : quant_int(cdc, 16);
                 q0 = (uint32_t) q;
-                flags &= ~1u;
                 if (active) S.dc[(mb + 1) * 6 + type] = q;
             }
             if (active) {
@@ -365,15 +367,16 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
                 cb[pos[0]] = (uint8_t) q0;
 #pragma unroll
                 for (int u = 1; u < 8; u++) cb[pos[u]] = (uint8_t) __float_as_uint(t[u]);
-            } else {
-                flags = 0;
             }
-            const unsigned any = __ballot_sync(0xffffffffu, flags != 0);
+            const bool mine = active && dist > gt;
+            const unsigned any = __ballot_sync(0xffffffffu, mine);
             if (any) {                // rare: remember which coefficients to redo exactly
-                if (flags) {
+                if (mine) {
                     unsigned long long m = 0;
+                    float tmp;
 #pragma unroll
-                    for (int u = 0; u < 8; u++) if (flags & (1u << u)) m |= 1ull << (8 * u + v);
+                    for (int u = 0; u < 8; u++)
+                        if ((u > 0 || v > 0) && quant_absdiff(d[u], gk[u], gc[u], tmp) > gt) m |= 1ull << (8 * u + v);
                     atomicOr(&S.amb[chunk], m);
                 }
                 const unsigned grp = (any >> (8 * jb)) & 0xffu;

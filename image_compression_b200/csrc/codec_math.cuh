@@ -236,15 +236,16 @@ AWI_HD int quant_int(int c, int Q) {
 // whose low mantissa byte is q in two's complement, and whether the result is ambiguous
 // (|g - q| > gt), i.e. the reference could have rounded the other way.  gc = 0 for even
 // quantiser steps: fma(x, gk, -+0) is then the plain rounded product.
-AWI_HD bool quant_flag(float x, float gk, float gc, float gt, float& t) {
+AWI_HD float quant_absdiff(float x, float gk, float gc, float& t) {      // |g - rn(g)|, and t = rn(g) + 1.5*2^23
     const float MAGIC = 12582912.0f;   // 1.5 * 2^23
     float sc = u2f(f2u(gc) | ((f2u(x) & 0x80000000u) ^ 0x80000000u));   // -sign(x)*gc
     float g = fma_rn(x, gk, sc);
     t = g + MAGIC;
     float n = t - MAGIC;
     float diff = g - n;
-    return (diff < 0 ? -diff : diff) > gt;
+    return diff < 0 ? -diff : diff;
 }
+AWI_HD bool quant_flag(float x, float gk, float gc, float gt, float& t) { return quant_absdiff(x, gk, gc, t) > gt; }
 
 // Fast DCT + quantise + scan-order pack of one 8x8 block held in registers.
 //   d[64]  in: centred samples, natural [y][x] order (destroyed)
