@@ -169,7 +169,7 @@ __device__ __forceinline__ void luma_row(const uint32_t* w, float* d) {
     if (any) {                                       // exact multiple of 1000 somewhere in the row: rare
 #pragma unroll
         for (int x = 0; x < 8; x++) {
-            if (n[x] % 1000u == 0u) {
+            if (n[x] * 4294968u < 2000000u) {          // same test as div1000
                 int b = byte_of(w[(3 * x) >> 2], (3 * x) & 3);
                 int g = byte_of(w[(3 * x + 1) >> 2], (3 * x + 1) & 3);
                 int r = byte_of(w[(3 * x + 2) >> 2], (3 * x + 2) & 3);
@@ -211,7 +211,8 @@ __device__ __forceinline__ void chroma_row(const uint32_t* w, float* d, int cBG,
     if (any) {
 #pragma unroll
         for (int x = 0; x < 8; x++) {
-            if (n[x] % 10000u == 0u) {
+            bool mult; (void) div10000(n[x], mult);
+            if (mult) {
                 int b = byte_of(w[(6 * x) >> 2], (6 * x) & 3);
                 int g = byte_of(w[(6 * x + 1) >> 2], (6 * x + 1) & 3);
                 int r = byte_of(w[(6 * x + 2) >> 2], (6 * x + 2) & 3);
@@ -242,12 +243,16 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
     // single-pass mode: ticketed tile order, so a tile only ever waits on tiles whose CTAs already run.
     // two-pass mode (staging buffer given): tiles are independent, any order will do.
     const bool two_pass = P.stage != nullptr;
-    if (tid == 0) { S.tile = two_pass ? (int) blockIdx.x : (int) atomicAdd(P.ticket, 1u); S.amb_count = 0; }
+    int tile = (int) blockIdx.x;
+    if (!two_pass) {                  // the ticket has to reach every thread: one extra barrier, single-pass mode only
+        if (tid == 0) S.tile = (int) atomicAdd(P.ticket, 1u);
+        __syncthreads();
+        tile = S.tile;
+    }
+    if (tid == 0) S.amb_count = 0;    // (these are first read after the barrier that ends phase A)
     if (tid < 64) S.cosf[tid] = __uint_as_float(cos_bits_rt(tid));
     if (tid < 6) S.halo_sum[tid] = 0;
     S.amb[tid] = 0;
-    __syncthreads();
-    const int tile = S.tile;
     // batches: tiles_per_frame tiles per frame, frames frame_stride bytes apart, predictors restart per frame
     const int frame = tile / P.tiles_per_frame, tile_in = tile - frame * P.tiles_per_frame;
     const int mb_first = P.mb0 + tile_in * TILE_MB;              // raster index inside the frame
@@ -355,16 +360,13 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
             float dist = v == 0 ? 0.0f : dist0;              // the DC (u = v = 0) is exact, never ambiguous
 #pragma unroll
             for (int u = 1; u < 8; u++) dist = fmaxf(dist, quant_absdiff(d[u], gk[u], gc[u], t[u]));
-            uint32_t q0 = __float_as_uint(t[0]);
-            if (v == 0) {             // exact DC: d[0] is the integer sum of the 64 centred samples
-                const int cdc = dc_coef_from_sum((int) d[0]);
-                const int q = chroma ? quant_int(cdc, 17) : quant_int(cdc, 16);
-                q0 = (uint32_t) q;
-                if (active) S.dc[(mb + 1) * 6 + type] = q;
-            }
             if (active) {
                 uint8_t* cb = coefb + chunk * 64;
-                cb[pos[0]] = (uint8_t) q0;
+                // lane v = 0 holds the DC position: d[0] there is the exact integer sum of the 64 centred
+                // samples (|S| <= 8192).  It is left as a sum; phase D turns sums into quantised DCs once per
+                // chunk (dct.c:50 + :123 in integers).  The magic add reads the integer without a conversion.
+                if (v == 0) S.dc[(mb + 1) * 6 + type] = __float_as_int(d[0] + 12582912.0f) - 0x4B400000;
+                else cb[pos[0]] = (uint8_t) __float_as_uint(t[0]);
 #pragma unroll
                 for (int u = 1; u < 8; u++) cb[pos[u]] = (uint8_t) __float_as_uint(t[u]);
             }
@@ -410,8 +412,7 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
     }
     __syncthreads();
 
-    if (tid < 6)
-        S.dc[tid] = has_halo ? quant_int(dc_coef_from_sum(S.halo_sum[tid] - 128 * 64), tid < 4 ? 16 : 17) : 0;
+    if (tid < 6) S.dc[tid] = has_halo ? S.halo_sum[tid] - 128 * 64 : 0;     // block sums, like every S.dc entry (sum 0 -> DC 0)
 
     // ---- C: exact recomputation of flagged coefficients (dct.c:26-53 operation order)
     const int n_amb = S.amb_count;
@@ -460,8 +461,10 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
         auto coef = [&](int i) -> int { return (int) cbase[coef_byte(tid, i)]; };
         uint32_t* slot = reinterpret_cast<uint32_t*>(S.raw + tid * SLOT);
         auto put = [&](int word, uint32_t be) { slot[word] = __byte_perm(be, 0, 0x0123); };
-        int dc = S.dc[(my_mb + 1) * 6 + my_type];
-        int prev = S.dc[my_mb * 6 + my_type];
+        const int c_dc = dc_coef_from_sum(S.dc[(my_mb + 1) * 6 + my_type]), c_prev = dc_coef_from_sum(S.dc[my_mb * 6 + my_type]);
+        const int dc = my_type >= 4 ? quant_int(c_dc, 17) : quant_int(c_dc, 16);             // constant divisors
+        const int prev = my_type >= 4 ? quant_int(c_prev, 17) : quant_int(c_prev, 16);
+        reinterpret_cast<int8_t*>(S.coef)[coef_byte(tid, 0)] = (int8_t) dc;       // for the optional coefficient output
         my_len = (uint32_t) rle_chunk(dc, prev, ((unsigned long long) hi << 32) | lo, coef, put);
     }
 
