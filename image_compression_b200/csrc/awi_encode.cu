@@ -412,7 +412,6 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
     }
     __syncthreads();
 
-    if (tid < 6) S.dc[tid] = has_halo ? S.halo_sum[tid] - 128 * 64 : 0;     // block sums, like every S.dc entry (sum 0 -> DC 0)
 
     // ---- C: exact recomputation of flagged coefficients (dct.c:26-53 operation order)
     const int n_amb = S.amb_count;
@@ -437,7 +436,8 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
             }
         }
     }
-    __syncthreads();                                   // raw pixels are dead from here on
+    if (n_amb > 0) __syncthreads();                    // (uniform) the fix-ups land before phase D; without any, the
+                                                       // barrier after phase B already separates the raw pixels from the slots
 
     // ---- D: run-length + bit packing, thread = chunk, into its slot
     uint32_t my_len = 0;
@@ -461,7 +461,9 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
         auto coef = [&](int i) -> int { return (int) cbase[coef_byte(tid, i)]; };
         uint32_t* slot = reinterpret_cast<uint32_t*>(S.raw + tid * SLOT);
         auto put = [&](int word, uint32_t be) { slot[word] = __byte_perm(be, 0, 0x0123); };
-        const int c_dc = dc_coef_from_sum(S.dc[(my_mb + 1) * 6 + my_type]), c_prev = dc_coef_from_sum(S.dc[my_mb * 6 + my_type]);
+        const int c_dc = dc_coef_from_sum(S.dc[(my_mb + 1) * 6 + my_type]), 
+                  c_prev = dc_coef_from_sum(my_mb > 0 ? S.dc[my_mb * 6 + my_type]                  // previous macroblock of the tile
+                                                      : (has_halo ? S.halo_sum[my_type] - 128 * 64 : 0));   // or the halo macroblock / frame start
         const int dc = my_type >= 4 ? quant_int(c_dc, 17) : quant_int(c_dc, 16);             // constant divisors
         const int prev = my_type >= 4 ? quant_int(c_prev, 17) : quant_int(c_prev, 16);
         reinterpret_cast<int8_t*>(S.coef)[coef_byte(tid, 0)] = (int8_t) dc;       // for the optional coefficient output
