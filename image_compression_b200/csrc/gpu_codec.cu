@@ -52,7 +52,10 @@ struct Ctx {
     int dev = -1;
     cudaStream_t stream = nullptr;            // compute (and small copies)
     cudaStream_t copy_stream = nullptr;       // bulk H2D / D2H overlapped with compute
+    cudaStream_t back_stream = nullptr;       // payload D2H while later sub-stripes are still uploading
     cudaEvent_t ev[MAX_SUB] = { nullptr };
+    cudaEvent_t ev_done[MAX_SUB] = { nullptr };
+    unsigned long long* h_chain = nullptr;    // pinned: payload length after each sub-stripe
     Buf enc_ws, enc_stage, dec_ws, in, out, frame_off;
     unsigned int* d_err = nullptr;
     unsigned long long* d_run = nullptr;      // running payload offset of a frame encoded in sub-stripes
@@ -87,7 +90,10 @@ void destroy_ctx(Ctx* c) {
     cudaSetDevice(c->dev);
     if (c->stream) cudaStreamDestroy(c->stream);
     if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
+    if (c->back_stream) cudaStreamDestroy(c->back_stream);
     for (cudaEvent_t e : c->ev) if (e) cudaEventDestroy(e);
+    for (cudaEvent_t e : c->ev_done) if (e) cudaEventDestroy(e);
+    if (c->h_chain) cudaFreeHost(c->h_chain);
     if (c->d_run) cudaFree(c->d_run);
     for (Buf* b : { &c->enc_ws, &c->enc_stage, &c->dec_ws, &c->in, &c->out, &c->frame_off })
         if (b->p) cudaFree(b->p);
@@ -98,8 +104,11 @@ void destroy_ctx(Ctx* c) {
 
 bool make_events(Ctx* c) {
     for (int i = 0; i < MAX_SUB; i++)
-        if (cudaEventCreateWithFlags(&c->ev[i], cudaEventDisableTiming) != cudaSuccess) return false;
-    return true;
+        if (cudaEventCreateWithFlags(&c->ev[i], cudaEventDisableTiming) != cudaSuccess ||
+            cudaEventCreateWithFlags(&c->ev_done[i], cudaEventDisableTiming) != cudaSuccess)
+            return false;
+    return cudaStreamCreateWithFlags(&c->back_stream, cudaStreamNonBlocking) == cudaSuccess &&
+           cudaMallocHost(&c->h_chain, MAX_SUB * 8) == cudaSuccess;
 }
 
 // Result buffers handed to the caller (`*payload`) come from a small pool of page-locked
@@ -458,7 +467,8 @@ bool gpu_codec_selftest_colour_dev(int ctx, const uint8_t* d_in, size_t n, int i
 // its length in *c->h_len after the compute stream drains.  The stripe's pixel rows are copied in
 // sub-stripes on the copy stream; each sub-stripe's kernels start as soon as its rows (and the
 // halo rows above them) have landed, so the PCIe transfer hides the compute.
-static bool encode_stripe_async(Ctx* c, const uint8_t* bmp_rows, int width, int height, int row_stride, int R0, int R1) {
+static bool encode_stripe_async(Ctx* c, const uint8_t* bmp_rows, int width, int height, int row_stride, int R0, int R1,
+                                int* n_sub_out = nullptr) {
     const int mbw = (width + 15) / 16;
     const int y_lo = R0 > 0 ? 16 * R0 - 16 : 0, y_hi = 16 * R1 < height ? 16 * R1 : height;
     const size_t in_bytes = (size_t) (y_hi - y_lo) * row_stride;
@@ -486,8 +496,55 @@ static bool encode_stripe_async(Ctx* c, const uint8_t* bmp_rows, int width, int 
         if (!encode_dev_impl(c, c->in.p, width, height, row_stride, y_lo, y_hi, r0, r1, c->out.p, cap, nullptr, nullptr,
                              nullptr, c->stream, c->d_run))
             return false;
+        CU(cudaMemcpyAsync(c->h_chain + s, c->d_run, 8, cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaEventRecord(c->ev_done[s], c->stream));
     }
     CU(cudaMemcpyAsync(c->h_len, c->d_run, 8, cudaMemcpyDeviceToHost, c->stream));
+    if (n_sub_out) *n_sub_out = n_sub;
+    return true;
+}
+
+// Single-device frame: ship each sub-stripe's payload bytes home as soon as its kernels are done, on a third
+// stream, while later sub-stripes are still uploading (PCIe is full duplex).  The result block is sized from
+// the first sub-stripe's yield; if the guess turns out too small the payload (still complete on the device) is
+// fetched again in one piece.
+static bool encode_frame_streamed(Ctx* c, const uint8_t* bmp_rows, int width, int height, int row_stride,
+                                  uint8_t** payload, size_t* payload_len) {
+    const int mbh = (height + 15) / 16;
+    int n_sub = 1;
+    if (!encode_stripe_async(c, bmp_rows, width, height, row_stride, 0, mbh, &n_sub)) return false;
+    uint8_t* buf = nullptr;
+    size_t cap = 0, prev = 0;
+    bool overflow = false;
+    for (int s = 0; s < n_sub; s++) {
+        CU(cudaEventSynchronize(c->ev_done[s]));
+        const size_t cur = (size_t) c->h_chain[s];
+        if (s == 0) {
+            cap = cur * (size_t) n_sub + cur * (size_t) n_sub / 2 + (1u << 20);
+            buf = static_cast<uint8_t*>(pool_get(cap));
+            if (!buf) return fail("encode: out of page-locked host memory (%zu bytes)", cap);
+        }
+        if (cur > cap || cur < prev) overflow = true;
+        if (!overflow && cur > prev) {
+            cudaError_t e = cudaMemcpyAsync(buf + prev, c->out.p + prev, cur - prev, cudaMemcpyDeviceToHost, c->back_stream);
+            if (e != cudaSuccess) { pool_put(buf); return fail("encode: D2H failed: %s", cudaGetErrorString(e)); }
+        }
+        prev = cur;
+    }
+    bool ok = check_err(c, c->stream, "encode");
+    const size_t total = ok ? (size_t) *c->h_len : 0;
+    if (ok && cudaStreamSynchronize(c->back_stream) != cudaSuccess) ok = fail("encode: D2H failed");
+    if (ok && overflow) {
+        pool_put(buf);
+        buf = static_cast<uint8_t*>(pool_get(total));
+        if (!buf) return fail("encode: out of page-locked host memory (%zu bytes)", total);
+        cudaError_t e = cudaMemcpyAsync(buf, c->out.p, total, cudaMemcpyDeviceToHost, c->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+        if (e != cudaSuccess) ok = fail("encode: D2H failed: %s", cudaGetErrorString(e));
+    }
+    if (!ok) { pool_put(buf); return false; }
+    *payload = buf;
+    *payload_len = total;
     return true;
 }
 
@@ -502,6 +559,7 @@ bool gpu_codec_encode_bgr(const uint8_t* bmp_rows, int width, int height, int ro
     const int G = (int) g_ctx.size() < mbh ? (int) g_ctx.size() : mbh;
     std::vector<std::unique_lock<std::mutex>> locks;
     for (int g = 0; g < G; g++) locks.emplace_back(g_ctx[g]->mu);
+    if (G == 1) return encode_frame_streamed(g_ctx[0], bmp_rows, width, height, row_stride, payload, payload_len);
 
     // phase 1: every GPU gets its stripe (+ the macroblock row above it) and encodes it
     for (int g = 0; g < G; g++) {
