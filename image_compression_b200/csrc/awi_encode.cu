@@ -82,6 +82,12 @@ __device__ __forceinline__ void st_desc(unsigned long long* p, unsigned long lon
 }
 
 // ---------------------------------------------------------------- phase A
+// pixels are read exactly once: stream them past L1
+__device__ __forceinline__ uint4 ld_stream(const uint4* p) {
+    uint4 v;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+    return v;
+}
 // bmp.c:48-119 addressing.  Pixel bytes outside the image read as zero (bmp.c:89-93,106-109).
 // `src` points at the piece; `valid` = bytes of it inside the image row (<= 0: none).
 __device__ __forceinline__ uint4 load_piece(const uint8_t* src, int valid, int align) {
@@ -276,7 +282,7 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
             const uint8_t* src = rows + (long long) (P.height - 1 - y0) * P.stride + xb;
             if (P.align == 16 && valid >= 16 && y0 + 14 < P.height) {     // the common case: 8 plain 128-bit loads
 #pragma unroll
-                for (int i = 0; i < 8; i++) v[i] = __ldg(reinterpret_cast<const uint4*>(src - (long long) (2 * i) * P.stride));
+                for (int i = 0; i < 8; i++) v[i] = ld_stream(reinterpret_cast<const uint4*>(src - (long long) (2 * i) * P.stride));
             } else {
 #pragma unroll
                 for (int i = 0; i < 8; i++)
