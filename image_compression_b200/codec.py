@@ -42,6 +42,7 @@ SYMBOLS = [
     ("gpu_codec_sync_check", C.c_bool, [C.c_int, C.c_void_p]),
     ("gpu_codec_synth_bgr_dev", C.c_bool, [C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_longlong, C.c_int, C.c_uint32,
                                            C.c_int, C.c_void_p]),
+    ("gpu_codec_selftest_tile_buffer", None, [C.c_int]),
     ("gpu_codec_selftest_colour_dev", C.c_bool, [C.c_int, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_void_p]),
 ]
 

@@ -503,7 +503,7 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
         __syncthreads();
     }
 
-    const bool compact_ok = total + 16 <= COMPACT_CAP;
+    const bool compact_ok = total + 16 <= (uint32_t) P.compact_cap;   // normally COMPACT_CAP; smaller only under the self-test hook
     uint8_t* compact = reinterpret_cast<uint8_t*>(S.coef);
 
     if (two_pass) {
@@ -723,6 +723,7 @@ cudaError_t launch_encode(const EncParams& P, int n_tiles, cudaStream_t stream) 
     }
     EncParams Q = P;
     Q.n_tiles = n_tiles;
+    if (Q.compact_cap <= 0 || Q.compact_cap > COMPACT_CAP) Q.compact_cap = COMPACT_CAP;
     if (Q.tiles_per_frame <= 0) { Q.tiles_per_frame = n_tiles; Q.frame_stride = 0; }      // a single frame
     awi_encode_kernel<<<n_tiles, THREADS, sizeof(EncSmem), stream>>>(Q);
     if (P.stage != nullptr) {

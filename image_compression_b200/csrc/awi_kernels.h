@@ -40,6 +40,7 @@ struct EncParams {
     long long frame_stride;       // batches: bytes between consecutive frames' pixel arrays
     unsigned long long* frame_off;  // batches, optional: n_frames+1 payload offsets (two-pass mode)
     int sm_count;                 // filled by launch_encode
+    int compact_cap;              // bytes of a tile that may be compacted in shared memory (0 = the built-in limit)
     int n_tiles;                  // filled by launch_encode: tiles of ENC_TILE_MB macroblocks covering the range
     uint8_t* out;                 // payload bytes for this range
     unsigned long long out_cap;

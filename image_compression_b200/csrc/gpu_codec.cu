@@ -63,6 +63,7 @@ struct Ctx {
     std::mutex mu;
 };
 
+int g_selftest_compact_cap = 0;           // see gpu_codec_selftest_tile_buffer
 std::vector<Ctx*> g_ctx;
 std::mutex g_mu;
 
@@ -261,6 +262,7 @@ bool encode_dev_impl(Ctx* c, const uint8_t* d_rows, int width, int height, long 
     P.tile_info = reinterpret_cast<uint2*>(c->enc_ws.p + ENC_WS_HEADER);
     P.tile_off = reinterpret_cast<unsigned long long*>(c->enc_ws.p + ENC_WS_HEADER + (size_t) n_tiles * 8);
     P.chain = d_chain;
+    P.compact_cap = g_selftest_compact_cap;
     P.tiles_per_frame = tiles_per_frame;
     P.frame_stride = frame_stride;
     P.frame_off = d_frame_off;
@@ -450,6 +452,8 @@ bool gpu_codec_synth_bgr_dev(int ctx, uint8_t* d_rows, int width, int height, lo
     CU(cudaGetLastError());
     return true;
 }
+
+void gpu_codec_selftest_tile_buffer(int bytes) { g_selftest_compact_cap = bytes > 0 ? bytes : 0; }
 
 bool gpu_codec_selftest_colour_dev(int ctx, const uint8_t* d_in, size_t n, int inverse, uint8_t* d_out, void* stream) {
     Ctx* c = get_ctx(ctx);
@@ -813,6 +817,7 @@ extern "C" bool gpu_codec_encode_bgr_dev_noalloc(const uint8_t* d_rows, int widt
     P.err = d_status;
     P.chunk_off = nullptr;
     P.qcoef = nullptr;
+    P.compact_cap = g_selftest_compact_cap;
     CU(awi::launch_encode(P, (int) n_tiles, st));
     return true;
 }

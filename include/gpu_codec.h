@@ -171,6 +171,11 @@ bool gpu_codec_synth_bgr_dev(int ctx, uint8_t* d_rows, int width, int height, lo
  * inverse == 0: (R,G,B) -> (Y,Cb,Cr) (color.c:31-33); else (Y,Cb,Cr) -> (R,G,B) (color.c:61-63). */
 bool gpu_codec_selftest_colour_dev(int ctx, const uint8_t* d_in, size_t n, int inverse, uint8_t* d_out, void* stream);
 
+/* Test hook: pretend the encoder's per-tile shared-memory buffer holds only `bytes` (0 restores the real
+ * 12 KB), which forces the chunk-by-chunk write path that otherwise needs > 64 bytes per chunk on average
+ * across a whole tile.  Results are unaffected.  No counterpart in the reference. */
+void gpu_codec_selftest_tile_buffer(int bytes);
+
 #ifdef __cplusplus
 }
 #endif

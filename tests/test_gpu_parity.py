@@ -247,3 +247,57 @@ def test_random_geometry_and_content(gpu, port):
         o = out.reshape(h, stride)
         assert (o[:, :3 * w] == ref_px[:, :3 * w]).all(), (trial, kind, w, h, stride)
         assert (o[:, 3 * w:] == 0xCD).all()     # row padding left untouched
+
+
+def test_long_chunk_write_path(gpu, port):
+    """Tiles whose chunks do not fit the compacted copy in shared memory take a chunk-by-chunk write path
+    (both output modes).  Natural content tops out near 56 bytes per chunk on average, below the 64 it takes,
+    so the self-test hook shrinks the buffer; saturated noise then overflows it in every tile."""
+    import torch
+    rng = np.random.default_rng(5)
+    lib = gpu.load()
+    try:
+        lib.gpu_codec_selftest_tile_buffer(4096)
+        for w, h in ((512, 64), (530, 100), (64, 16)):
+            stride = synth.bmp_stride(w)
+            rgb = (rng.integers(0, 2, (h, w, 3)) * 255).astype(np.uint8)
+            rows = synth.rows_from_rgb_topdown(rgb)
+            want, _, lens = port.encode_bgr(rows, w, h, stride, want_coefs=True)
+            assert lens.mean() > 40                                   # 192 chunks x 40 B > 4096: every full tile overflows
+            assert gpu.encode_bgr(rows, w, h, stride) == want.tobytes()
+            rows_t = torch.from_numpy(rows.reshape(-1)).cuda()
+            p, off, _ = _dev_encode(gpu, rows_t, w, h, stride)
+            assert p.tobytes() == want.tobytes()
+            assert (off == np.concatenate([[0], np.cumsum(lens)[:-1]])).all()
+            # single-pass (look-back) mode through the no-alloc entry point
+            payload = torch.empty(gpu.max_payload_bytes(w, h) + 16, dtype=torch.uint8, device="cuda")
+            n = torch.zeros(1, dtype=torch.int64, device="cuda")
+            status = torch.zeros(1, dtype=torch.int32, device="cuda")
+            gpu.encode_dev_noalloc(rows_t, w, h, stride, payload, n, status)
+            torch.cuda.synchronize()
+            assert int(status.item()) == 0 and payload[: int(n.item())].cpu().numpy().tobytes() == want.tobytes()
+    finally:
+        lib.gpu_codec_selftest_tile_buffer(0)
+
+
+def test_degenerate_arguments_are_refused(gpu):
+    from image_compression_b200 import codec
+    rows = np.zeros(48, np.uint8)
+    for w, h, stride in ((0, 4, 12), (4, 0, 12), (4, 4, 8), (-1, 4, 12)):
+        with pytest.raises(codec.GpuCodecError):
+            gpu.encode_bgr(np.zeros(max(1, abs(stride) * max(1, h)), np.uint8), w, h, stride)
+    with pytest.raises(codec.GpuCodecError):
+        gpu.decode_to_bgr(np.zeros(0, np.uint8), 16, 16)          # empty payload
+    with pytest.raises(codec.GpuCodecError):
+        gpu.decode_to_bgr(np.zeros(17, np.uint8), 16, 16)         # shorter than six minimal chunks
+    assert gpu.encode_bgr(rows, 4, 4, 12)                          # still alive
+
+
+def test_extreme_aspect_ratios(gpu, port):
+    for w, h in ((40000, 16), (16, 40000), (65535, 1), (1, 30000)):
+        stride = synth.bmp_stride(w)
+        rows = synth.frame_bgr_bottomup("photo", w, h, 0xA11CE06)
+        want = port.encode_bgr(rows, w, h, stride)
+        got = gpu.encode_bgr(rows, w, h, stride)
+        assert got == want.tobytes(), (w, h)
+        assert gpu.decode_to_bgr(got, w, h, stride).tobytes() == port.decode(want, w, h, stride)[0].tobytes()
