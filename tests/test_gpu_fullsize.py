@@ -59,10 +59,8 @@ def test_16k_properties(gpu, port, kind):
     for r0, r1 in ((0, 2), (511, 514)):
         y0, y1 = stripes.stripe_window(h, r0, r1)
         b0, b1 = stripes.window_byte_range(h, stride, y0, y1)
-        band = np.zeros(1, np.uint8)
         # hand the oracle a virtual full frame: only the window is populated
         win = t[b0:b1].cpu().numpy()
-        full = np.lib.stride_tricks.as_strided(win, shape=(win.size,), strides=(1,))
         want = port_encode_window(port, win, w, h, stride, y0, y1, r0, r1)
         lo = offs[r0 * mbw * 6]
         hi = offs[r1 * mbw * 6] if r1 < mbh else p.numel()
