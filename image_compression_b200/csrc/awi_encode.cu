@@ -240,6 +240,29 @@ __device__ __forceinline__ int sample_of(const EncSmem& S, int chunk, int y, int
     return chroma_of(r, g, b, type == 5);
 }
 
+#ifdef ENC_PHASE_CLOCKS
+// debug build only (tools/phase_clocks.py): cycles per warp between phase marks, summed over all tiles.
+// Kept in registers and added to one of 128 copies at the end, so the marks do not crowd one L2 slice.
+__device__ unsigned long long g_phase_clk[128][16][8];
+__device__ __forceinline__ long long phase_clock() { long long t; asm volatile("mov.u64 %0, %%clock64;" : "=l"(t) :: "memory"); return t; }
+#define PHASE_INIT() long long t_prev_ = phase_clock(); unsigned int ph_[13] = {}
+#define PHASE_MARK(i) do { long long t_now_ = phase_clock(); ph_[i] = (unsigned int) (t_now_ - t_prev_); t_prev_ = t_now_; \
+        if ((i) == 12 && lane == 0) { for (int q_ = 0; q_ < 13; q_++) atomicAdd(&g_phase_clk[blockIdx.x & 127][q_][warp], (unsigned long long) ph_[q_]); } } while (0)
+extern "C" int awi_debug_phase_clocks(unsigned long long* out, int reset) {
+    static unsigned long long h[128][16][8];
+    if (out) {
+        if (cudaMemcpyFromSymbol(h, g_phase_clk, sizeof(h)) != cudaSuccess) return 0;
+        for (int i = 0; i < 128; i++) out[i] = 0;
+        for (int c = 0; c < 128; c++) for (int i = 0; i < 16; i++) for (int w = 0; w < 8; w++) out[i * 8 + w] += h[c][i][w];
+    }
+    if (reset) { for (auto& c : h) for (auto& r : c) for (auto& v : r) v = 0; if (cudaMemcpyToSymbol(g_phase_clk, h, sizeof(h)) != cudaSuccess) return 0; }
+    return 1;
+}
+#else
+#define PHASE_MARK(i) do { } while (0)
+#define PHASE_INIT() do { } while (0)
+#endif
+
 // ---------------------------------------------------------------- the kernel
 __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncParams P) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -248,6 +271,7 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
 
     // single-pass mode: ticketed tile order, so a tile only ever waits on tiles whose CTAs already run.
     // two-pass mode (staging buffer given): tiles are independent, any order will do.
+    PHASE_INIT();
     const bool two_pass = P.stage != nullptr;
     int tile = (int) blockIdx.x;
     if (!two_pass) {                  // the ticket has to reach every thread: one extra barrier, single-pass mode only
@@ -304,7 +328,9 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
             reinterpret_cast<uint4*>(S.halo)[tid] = h;
         }
     }
+    PHASE_MARK(0);
     __syncthreads();
+    PHASE_MARK(1);
 
     // ---- B: colour + DCT + quantise; 8 lanes per block, 4 blocks per warp per iteration
     {
@@ -393,6 +419,7 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
         }
     }
 
+    PHASE_MARK(2);
     // halo macroblock: only the six block sums are needed (integer DC formula)
     if (has_halo) {
         if (tid < 128) {
@@ -416,8 +443,9 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
             if (lane == 0) { atomicAdd(&S.halo_sum[4], cb); atomicAdd(&S.halo_sum[5], cr); }
         }
     }
+    PHASE_MARK(3);
     __syncthreads();
-
+    PHASE_MARK(4);
 
     // ---- C: exact recomputation of flagged coefficients (dct.c:26-53 operation order)
     const int n_amb = S.amb_count;
@@ -442,9 +470,11 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
             }
         }
     }
+    PHASE_MARK(5);
     if (n_amb > 0) __syncthreads();                    // (uniform) the fix-ups land before phase D; without any, the
                                                        // barrier after phase B already separates the raw pixels from the slots
 
+    PHASE_MARK(6);
     // ---- D: run-length + bit packing, thread = chunk, into its slot
     uint32_t my_len = 0;
     const int my_mb = tid / 6, my_type = tid - 6 * my_mb;
@@ -476,6 +506,7 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
         my_len = (uint32_t) rle_chunk(dc, prev, ((unsigned long long) hi << 32) | lo, coef, put);
     }
 
+    PHASE_MARK(7);
     // ---- E: offsets inside the tile
     uint32_t total, my_off;
     {
@@ -486,6 +517,7 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
             if (lane >= o) incl += t;
         }
         if (lane == 31) S.warp_tot[warp] = incl;
+        PHASE_MARK(8);
         __syncthreads();                                // also: every slot written, coefficients no longer read by D
         uint32_t wbase = 0;
         total = 0;
@@ -493,6 +525,7 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
         for (int i = 0; i < NWARPS; i++) { uint32_t t = S.warp_tot[i]; if (i < warp) wbase += t; total += t; }
         my_off = wbase + incl - my_len;
     }
+    PHASE_MARK(9);
     // optional per-chunk outputs (tests, decode side-info) need the coefficient buffer: before it is reused
     if (P.qcoef != nullptr) {
         if (my_mb < n_mb) {
@@ -521,7 +554,9 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
             uint8_t* dst = compact + my_off;
             for (uint32_t i = 0; i < my_len; i++) dst[i] = src[i];
         }
+        PHASE_MARK(10);
         __syncthreads();
+        PHASE_MARK(11);
         const unsigned long long at = S.tile_base;
         const bool fits = at + ((total + 15u) >> 4) <= P.stage_cap_units;
         if (P.chunk_off != nullptr && my_mb < n_mb)
@@ -537,6 +572,7 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
                 for (uint32_t i = 0; i < my_len; i++) out[my_off + i] = src[i];
             }
         }
+        PHASE_MARK(12);
         return;
     }
 
