@@ -28,6 +28,7 @@
 #include <stdint.h>
 #include "codec_math.cuh"
 #include "awi_kernels.h"
+#include <type_traits>
 
 namespace awi {
 
@@ -53,7 +54,6 @@ struct __align__(16) EncSmem {
     uint32_t coef[THREADS * 16];                 // int8[64] per chunk, scan order; phase E-F: compacted tile
     float tr[NWARPS][TR_WORDS];                  // phase B transposes
     unsigned long long amb[THREADS];             // per chunk: natural positions to recompute
-    float cosf[64];
     int dc[(TILE_MB + 1) * 6];                   // quantised DCs, [0] = halo macroblock
     int halo_sum[6];
     uint32_t len[THREADS];                       // chunk byte lengths, chunk order
@@ -280,7 +280,6 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
         tile = S.tile;
     }
     if (tid == 0) S.amb_count = 0;    // (these are first read after the barrier that ends phase A)
-    if (tid < 64) S.cosf[tid] = __uint_as_float(cos_bits_rt(tid));
     if (tid < 6) S.halo_sum[tid] = 0;
     S.amb[tid] = 0;
     // batches: tiles_per_frame tiles per frame, frames frame_stride bytes apart, predictors restart per frame
@@ -313,54 +312,51 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
                     if (y0 + 2 * i < P.height) v[i] = load_piece(src - (long long) (2 * i) * P.stride, valid, P.align);
             }
         }
+        // the halo macroblock's piece is requested before anything waits on the tile's own loads
+        uint4 h = make_uint4(0, 0, 0, 0);
+        if (tid < 48 && has_halo) {
+            const int g = mb_first - 1, row = tid / 3, kk = tid - 3 * row;
+            const int my = g / P.mbw, mx = g - my * P.mbw;
+            const int xb = mx * 48 + kk * 16, y = my * 16 + row;
+            if (y < P.height)
+                h = load_piece(rows + (long long) (P.height - 1 - y) * P.stride + xb, P.width * 3 - xb, P.align);
+        }
         uint8_t* dst = S.raw + r0 * PITCH + col * 16;
 #pragma unroll
         for (int i = 0; i < 8; i++) *reinterpret_cast<uint4*>(dst + i * 2 * PITCH) = v[i];
-        if (tid < 48) {
-            uint4 h = make_uint4(0, 0, 0, 0);
-            if (has_halo) {
-                const int g = mb_first - 1, row = tid / 3, kk = tid - 3 * row;
-                const int my = g / P.mbw, mx = g - my * P.mbw;
-                const int xb = mx * 48 + kk * 16, y = my * 16 + row;
-                if (y < P.height)
-                    h = load_piece(rows + (long long) (P.height - 1 - y) * P.stride + xb, P.width * 3 - xb, P.align);
-            }
-            reinterpret_cast<uint4*>(S.halo)[tid] = h;
-        }
+        if (tid < 48) reinterpret_cast<uint4*>(S.halo)[tid] = h;
     }
     PHASE_MARK(0);
     __syncthreads();
     PHASE_MARK(1);
 
-    // ---- B: colour + DCT + quantise; 8 lanes per block, 4 blocks per warp per iteration
+    // ---- B: colour + DCT + quantise; 8 lanes per block, 4 blocks per warp per iteration.
+    //      48 iterations per tile (32 of luma blocks, 16 of Cb/Cr pairs) are dealt round-robin to the six
+    //      warps, so every warp gets the same mix and they reach the barrier together.
     {
         const int v = lane & 7, jb = lane >> 3;                   // v: my row in pass 1, my column in pass 2
-        const bool chroma = warp >= 4;
         // per-lane quantiser constants for natural positions (u, v), u = 0..7, and where
         // their quantised values go in the chunk
         float gk[8], gc[8];
         int pos[8];                                               // scan positions of my 8 coefficients
 #pragma unroll
-        for (int u = 0; u < 8; u++) {
-            gk[u] = d_gk[chroma][8 * u + v];
-            gc[u] = d_gc[chroma][8 * u + v];
-            pos[u] = unscan_rt(8 * u + v);
-        }
-        // one ambiguity threshold for every position (the tightest of the table): a few more exact
-        // recomputations, but the per-coefficient test is a running maximum and 8 registers are saved
-        const float gt = chroma ? AWI_GT_MIN_CHROMA : AWI_GT_MIN_LUMA;
+        for (int u = 0; u < 8; u++) pos[u] = unscan_rt(8 * u + v);
         float* tr = S.tr[warp];
         uint8_t* coefb = reinterpret_cast<uint8_t*>(S.coef);
         const int cBG = jb & 1 ? pack16(-813, -4187) : pack16(5000, -3313), cR = jb & 1 ? pack16(5000, 0) : pack16(-1687, 0);
 
-        for (int it = 0; it < 8; it++) {
+        auto iteration = [&](auto kind, int j) {
+            constexpr bool chroma = decltype(kind)::value;
+            // one ambiguity threshold for every position (the tightest of the table): a few more exact
+            // recomputations, but the per-coefficient test is a running maximum and 8 registers are saved
+            constexpr float gt = chroma ? AWI_GT_MIN_CHROMA : AWI_GT_MIN_LUMA;
             int mb, type;
-            if (!chroma) {            // warp = 2*half + block-row; 32 horizontally adjacent blocks per warp
-                const int c = ((warp >> 1) << 5) + 4 * it + jb;
+            if (!chroma) {            // j = 16*half + 8*block-row + it; 32 horizontally adjacent blocks per (half, block-row)
+                const int c = ((j >> 4) << 5) + 4 * (j & 7) + jb;
                 mb = c >> 1;
-                type = ((warp & 1) << 1) | (c & 1);
-            } else {                  // 16 macroblocks per warp, (Cb, Cr) pairs
-                mb = ((warp - 4) << 4) + 2 * it + (jb >> 1);
+                type = (((j >> 3) & 1) << 1) | (c & 1);
+            } else {                  // (Cb, Cr) pairs of two macroblocks
+                mb = 2 * j + (jb >> 1);
                 type = 4 + (jb & 1);
             }
             const int chunk = mb * 6 + type;
@@ -416,7 +412,13 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
                 const unsigned grp = (any >> (8 * jb)) & 0xffu;
                 if (grp && v == __ffs((int) grp) - 1) S.amb_list[atomicAdd(&S.amb_count, 1)] = (uint16_t) chunk;
             }
-        }
+        };
+#pragma unroll
+        for (int u = 0; u < 8; u++) { gk[u] = d_gk[0][8 * u + v]; gc[u] = d_gc[0][8 * u + v]; }
+        for (int j = warp; j < TILE_MB; j += NWARPS) iteration(std::false_type{}, j);
+#pragma unroll
+        for (int u = 0; u < 8; u++) { gk[u] = d_gk[1][8 * u + v]; gc[u] = d_gc[1][8 * u + v]; }
+        for (int j = (warp + 4) % NWARPS; j < TILE_MB / 2; j += NWARPS) iteration(std::true_type{}, j);
     }
 
     PHASE_MARK(2);
@@ -458,9 +460,9 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
             m &= m - 1;
             int u = k >> 3, v = k & 7;
             int y = lane >> 2, x0 = (lane & 3) * 2;
-            float cyu = S.cosf[y * 8 + u];
-            double part = (double) exact_product(sample_of(S, b, y, x0) - 128, cyu, S.cosf[x0 * 8 + v]);
-            part += (double) exact_product(sample_of(S, b, y, x0 + 1) - 128, cyu, S.cosf[(x0 + 1) * 8 + v]);
+            float cyu = __uint_as_float(cos_bits_rt(y * 8 + u));
+            double part = (double) exact_product(sample_of(S, b, y, x0) - 128, cyu, __uint_as_float(cos_bits_rt(x0 * 8 + v)));
+            part += (double) exact_product(sample_of(S, b, y, x0 + 1) - 128, cyu, __uint_as_float(cos_bits_rt((x0 + 1) * 8 + v)));
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
             if (lane == 0) {
