@@ -43,7 +43,7 @@ constexpr int PITCH = TILE_MB * 48 + 16;         // smem bytes per pixel row: 38
 constexpr int RAW_BYTES = 16 * PITCH;            // 24832
 constexpr int SLOT = 124;                        // staging bytes per chunk (max 121), 31 words: conflict-free
 constexpr int COMPACT_CAP = THREADS * 64;        // compacted tile lives in the (dead) coefficient buffer
-constexpr int TR_WORDS = 4 * 72;                 // per warp: 4 blocks x 8 rows x (8 + 1 pad) floats
+constexpr int TR_WORDS = 4 * 72;                 // per warp: 4 blocks x (8 rows x 8 floats + 8 pad)
 static_assert(THREADS * SLOT <= RAW_BYTES, "chunk slots alias the raw tile");
 static_assert(THREADS == 2 * TILE_MB * 3, "loader: one fixed (macroblock, 16-byte piece) per thread, two rows per pass");
 static_assert(THREADS == TILE_MB * 6, "one thread per chunk in phases D-F");
@@ -341,7 +341,11 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
         int pos[8];                                               // scan positions of my 8 coefficients
 #pragma unroll
         for (int u = 0; u < 8; u++) pos[u] = unscan_rt(8 * u + v);
-        float* tr = S.tr[warp];
+        float* tr = S.tr[warp];                                   // 4 blocks x 72 floats: 8 rows of 8, block stride 8 mod 32
+        float4* const tr_row = reinterpret_cast<float4*>(tr + jb * 72 + v * 8);
+        const int tr_sw = v >> 2;
+        const float* const tr_col0 = tr + jb * 72 + v;
+        const float* const tr_col1 = tr + jb * 72 + (v ^ 4);
         uint8_t* coefb = reinterpret_cast<uint8_t*>(S.coef);
         const int cBG = jb & 1 ? pack16(-813, -4187) : pack16(5000, -3313), cR = jb & 1 ? pack16(5000, 0) : pack16(-1687, 0);
 
@@ -375,12 +379,16 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
                 chroma_row(w, d, cBG, cR, jb & 1);
             }
             aan8(d[0], d[1], d[2], d[3], d[4], d[5], d[6], d[7]);                 // row pass
+            // transpose through shared memory: a row goes out as two 128-bit stores (the halves swap places in
+            // rows 4-7, so the eight rows of a block cover all 32 banks), a column comes back as 8 scalar loads
+            __syncwarp();
+            tr_row[tr_sw] = make_float4(d[0], d[1], d[2], d[3]);
+            tr_row[tr_sw ^ 1] = make_float4(d[4], d[5], d[6], d[7]);
             __syncwarp();
 #pragma unroll
-            for (int x = 0; x < 8; x++) tr[jb * 72 + v * 9 + x] = d[x];
-            __syncwarp();
+            for (int u = 0; u < 4; u++) d[u] = tr_col0[8 * u];
 #pragma unroll
-            for (int u = 0; u < 8; u++) d[u] = tr[jb * 72 + u * 9 + v];
+            for (int u = 4; u < 8; u++) d[u] = tr_col1[8 * u];
             aan8(d[0], d[1], d[2], d[3], d[4], d[5], d[6], d[7]);                 // column pass: d[u] = coefficient (u, v)
 
             float t[8];

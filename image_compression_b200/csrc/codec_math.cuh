@@ -338,23 +338,34 @@ AWI_HD int lowest_set64(uint64_t m) {
 #endif
 }
 
+AWI_HD int lowest_set32(uint32_t m) {
+#if defined(__CUDA_ARCH__)
+    return __ffs((int) m) - 1;
+#else
+    return __builtin_ctz(m);
+#endif
+}
+
 template <class Coef, class Put>
 AWI_HD int rle_chunk(int dc, int prev_dc, uint64_t nzmask, Coef coef, Put put32) {
     BitAcc s;
     int diff = dc - prev_dc;
     bits_push(s, (uint32_t) (diff >= 0 ? diff : 4095 + diff) & 0xFFFu, 12, put32);      // rle.c:53-57
-    int prev = 0;
-    uint64_t m = nzmask & ~1ull;
-    while (m) {
-        int i = lowest_set64(m);
+    int prev = 0, base = 0;
+    uint32_t m = (uint32_t) nzmask & ~1u, next = (uint32_t) (nzmask >> 32);             // positions 1..31, then 32..63
+    while (true) {
+        if (m == 0) {
+            if (next == 0) break;
+            m = next; next = 0; base = 32;
+        }
+        int i = base + lowest_set32(m);
         m &= m - 1;
         int gap = i - prev - 1;
         prev = i;
         for (int z = gap >> 4; z > 0; z--) bits_push(s, 0xF0u, 8, put32);               // rle.c:70-83
         int v = coef(i);
-        uint32_t a = (uint32_t) (v < 0 ? -v : v);
-        int size = bit_length_u(a);
-        uint32_t field = v > 0 ? (uint32_t) v : (uint32_t) ((1 << size) - 1 + v);       // rle.c:86-92
+        int size = bit_length_u((uint32_t) (v < 0 ? -v : v));
+        uint32_t field = (uint32_t) (v + (v >> 31)) & ((1u << size) - 1u);              // rle.c:86-92: v, or v - 1 in `size` bits
         bits_push(s, ((uint32_t) ((gap & 15) << 4 | size) << size) | field, 8 + size, put32);
     }
     bits_push(s, 0u, 8, put32);                                                          // EOB, rle.c:106
