@@ -36,7 +36,7 @@ namespace awi {
 #define ENC_MIN_CTAS 4                           // resident CTAs per SM the register budget is sized for
 #endif
 constexpr int TILE_MB = ENC_TILE_MB;             // 32 macroblocks per tile
-constexpr int THREADS = 192;                     // = chunks per tile; phase B: 24 blocks-at-a-time of 8 lanes
+constexpr int THREADS = TILE_MB * 6;              // = chunks per tile; phase B: 4 blocks at a time per warp, 8 lanes each
 constexpr int NWARPS = THREADS / 32;
 constexpr int PITCH = TILE_MB * 48 + 16;         // smem bytes per pixel row: 388 words = 4 mod 32 -> the 8 rows of a
                                                  // block land 4 banks apart, conflict-free 64-bit row reads
@@ -426,31 +426,34 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
         for (int j = warp; j < TILE_MB; j += NWARPS) iteration(std::false_type{}, j);
 #pragma unroll
         for (int u = 0; u < 8; u++) { gk[u] = d_gk[1][8 * u + v]; gc[u] = d_gc[1][8 * u + v]; }
-        for (int j = (warp + 4) % NWARPS; j < TILE_MB / 2; j += NWARPS) iteration(std::true_type{}, j);
+        for (int j = (warp + NWARPS - TILE_MB % NWARPS) % NWARPS; j < TILE_MB / 2; j += NWARPS) iteration(std::true_type{}, j);
     }
 
     PHASE_MARK(2);
     // halo macroblock: only the six block sums are needed (integer DC formula)
     if (has_halo) {
-        if (tid < 128) {
-            int p = 2 * tid, py = p >> 4, px = p & 15;
-            const uint8_t* q = S.halo + py * 48 + px * 3;
-            int s = luma_of(q[2], q[1], q[0]) + luma_of(q[5], q[4], q[3]);
-            s += __shfl_xor_sync(0xffffffffu, s, 1);
-            s += __shfl_xor_sync(0xffffffffu, s, 2);
-            s += __shfl_xor_sync(0xffffffffu, s, 8);
-            s += __shfl_xor_sync(0xffffffffu, s, 16);
-            if ((lane & 27) == 0) atomicAdd(&S.halo_sum[((py >> 3) << 1) | (px >> 3)], s);
-        } else {
-            int t = tid - 128, yy = t >> 3, xx = t & 7;
-            const uint8_t* q = S.halo + 2 * yy * 48 + 6 * xx;
-            int cb = chroma_of(q[2], q[1], q[0], false), cr = chroma_of(q[2], q[1], q[0], true);
+        // 192 work items in whole warps: 128 pixel pairs for the four luma sums, 64 pixels for the two chroma sums
+        for (int item = tid; item < 192; item += THREADS) {
+            if (item < 128) {
+                int p = 2 * item, py = p >> 4, px = p & 15;
+                const uint8_t* q = S.halo + py * 48 + px * 3;
+                int s = luma_of(q[2], q[1], q[0]) + luma_of(q[5], q[4], q[3]);
+                s += __shfl_xor_sync(0xffffffffu, s, 1);
+                s += __shfl_xor_sync(0xffffffffu, s, 2);
+                s += __shfl_xor_sync(0xffffffffu, s, 8);
+                s += __shfl_xor_sync(0xffffffffu, s, 16);
+                if ((lane & 27) == 0) atomicAdd(&S.halo_sum[((py >> 3) << 1) | (px >> 3)], s);
+            } else {
+                int t = item - 128, yy = t >> 3, xx = t & 7;
+                const uint8_t* q = S.halo + 2 * yy * 48 + 6 * xx;
+                int cb = chroma_of(q[2], q[1], q[0], false), cr = chroma_of(q[2], q[1], q[0], true);
 #pragma unroll
-            for (int o = 16; o > 0; o >>= 1) {
-                cb += __shfl_xor_sync(0xffffffffu, cb, o);
-                cr += __shfl_xor_sync(0xffffffffu, cr, o);
+                for (int o = 16; o > 0; o >>= 1) {
+                    cb += __shfl_xor_sync(0xffffffffu, cb, o);
+                    cr += __shfl_xor_sync(0xffffffffu, cr, o);
+                }
+                if (lane == 0) { atomicAdd(&S.halo_sum[4], cb); atomicAdd(&S.halo_sum[5], cr); }
             }
-            if (lane == 0) { atomicAdd(&S.halo_sum[4], cb); atomicAdd(&S.halo_sum[5], cr); }
         }
     }
     PHASE_MARK(3);

@@ -8,7 +8,10 @@
 
 namespace awi {
 
-constexpr int ENC_TILE_MB = 32;      // macroblocks per encode tile (one CTA)
+#ifndef ENC_TILE_MB_N
+#define ENC_TILE_MB_N 32
+#endif
+constexpr int ENC_TILE_MB = ENC_TILE_MB_N;      // macroblocks per encode tile (one CTA)
 
 // Run-time indexed copies of the generated tables (device global memory; the hot loops
 // use the constexpr accessors in codec_math.cuh, which fold into immediates).

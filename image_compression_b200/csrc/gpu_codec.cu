@@ -519,25 +519,27 @@ static bool encode_frame_streamed(Ctx* c, const uint8_t* bmp_rows, int width, in
     if (!encode_stripe_async(c, bmp_rows, width, height, row_stride, 0, mbh, &n_sub)) return false;
     uint8_t* buf = nullptr;
     size_t cap = 0, prev = 0;
-    bool overflow = false;
-    for (int s = 0; s < n_sub; s++) {
-        CU(cudaEventSynchronize(c->ev_done[s]));
+    bool overflow = false, ok = true;
+    for (int s = 0; s < n_sub && ok; s++) {
+        cudaError_t e = cudaEventSynchronize(c->ev_done[s]);
+        if (e != cudaSuccess) { ok = fail("encode: waiting for sub-stripe %d failed: %s", s, cudaGetErrorString(e)); break; }
         const size_t cur = (size_t) c->h_chain[s];
         if (s == 0) {
             cap = cur * (size_t) n_sub + cur * (size_t) n_sub / 2 + (1u << 20);
             buf = static_cast<uint8_t*>(pool_get(cap));
-            if (!buf) return fail("encode: out of page-locked host memory (%zu bytes)", cap);
+            if (!buf) { ok = fail("encode: out of page-locked host memory (%zu bytes)", cap); break; }
         }
         if (cur > cap || cur < prev) overflow = true;
         if (!overflow && cur > prev) {
-            cudaError_t e = cudaMemcpyAsync(buf + prev, c->out.p + prev, cur - prev, cudaMemcpyDeviceToHost, c->back_stream);
-            if (e != cudaSuccess) { pool_put(buf); return fail("encode: D2H failed: %s", cudaGetErrorString(e)); }
+            e = cudaMemcpyAsync(buf + prev, c->out.p + prev, cur - prev, cudaMemcpyDeviceToHost, c->back_stream);
+            if (e != cudaSuccess) ok = fail("encode: D2H failed: %s", cudaGetErrorString(e));
         }
         prev = cur;
     }
-    bool ok = check_err(c, c->stream, "encode");
+    if (!check_err(c, c->stream, "encode")) ok = false;      // also drains the compute stream on the failure paths
     const size_t total = ok ? (size_t) *c->h_len : 0;
-    if (ok && cudaStreamSynchronize(c->back_stream) != cudaSuccess) ok = fail("encode: D2H failed");
+    // the block may only change hands once nothing is being copied into it any more
+    if (cudaStreamSynchronize(c->back_stream) != cudaSuccess && ok) ok = fail("encode: D2H failed");
     if (ok && overflow) {
         pool_put(buf);
         buf = static_cast<uint8_t*>(pool_get(total));
@@ -546,7 +548,7 @@ static bool encode_frame_streamed(Ctx* c, const uint8_t* bmp_rows, int width, in
         if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
         if (e != cudaSuccess) ok = fail("encode: D2H failed: %s", cudaGetErrorString(e));
     }
-    if (!ok) { pool_put(buf); return false; }
+    if (!ok) { if (buf) pool_put(buf); return false; }
     *payload = buf;
     *payload_len = total;
     return true;
@@ -558,7 +560,7 @@ bool gpu_codec_encode_bgr(const uint8_t* bmp_rows, int width, int height, int ro
     *payload = nullptr;
     *payload_len = 0;
     if (g_ctx.empty()) return fail("encode: not initialised (call gpu_codec_init)");
-    if (!bmp_rows || width <= 0 || height <= 0 || row_stride < 3 * width) return fail("encode: bad arguments");
+    if (!bmp_rows || width <= 0 || height <= 0 || row_stride < 3ll * width) return fail("encode: bad arguments");
     const int mbh = (height + 15) / 16;
     const int G = (int) g_ctx.size() < mbh ? (int) g_ctx.size() : mbh;
     std::vector<std::unique_lock<std::mutex>> locks;
@@ -646,6 +648,7 @@ static bool encode_batch_on_ctx(Ctx* c, const uint8_t* const* frames, int n_fram
         return true;
     };
     ok = ok && body();
+    if (!ok) cudaStreamSynchronize(c->stream);           // nothing may still be copying into blocks the caller is about to release
     if (h_off) pool_put(h_off);
     return ok;
 }
@@ -653,7 +656,7 @@ static bool encode_batch_on_ctx(Ctx* c, const uint8_t* const* frames, int n_fram
 bool gpu_codec_encode_batch_bgr(const uint8_t* const* frames, int n_frames, int width, int height, int row_stride,
                                 uint8_t** payloads, size_t* payload_lens) {
     if (g_ctx.empty()) return fail("encode_batch: not initialised (call gpu_codec_init)");
-    if (!frames || !payloads || !payload_lens || n_frames < 0 || width <= 0 || height <= 0 || row_stride < 3 * width)
+    if (!frames || !payloads || !payload_lens || n_frames < 0 || width <= 0 || height <= 0 || row_stride < 3ll * width)
         return fail("encode_batch: bad arguments");
     for (int i = 0; i < n_frames; i++) { payloads[i] = nullptr; payload_lens[i] = 0; }
     const int G = (int) g_ctx.size();
@@ -686,7 +689,7 @@ static bool decode_host(const uint8_t* payload, size_t len, int width, int heigh
     const long long pitch = rgb ? 3ll * width : stride;
     std::vector<std::unique_lock<std::mutex>> locks;
     for (int g = 0; g < G; g++) locks.emplace_back(g_ctx[g]->mu);
-    for (int g = 0; g < G; g++) {
+    auto enqueue = [&](int g) -> bool {
         Ctx* c = g_ctx[g];
         int R0, R1;
         stripe_rows(mbh, g, G, R0, R1);
@@ -718,8 +721,11 @@ static bool decode_host(const uint8_t* payload, size_t len, int width, int heigh
                                      cudaMemcpyDeviceToHost, c->copy_stream));
             }
         }
-    }
+        return true;
+    };
     bool ok = true;
+    for (int g = 0; g < G && ok; g++) ok = enqueue(g);
+    // success or not, nothing may still be writing into the caller's buffer when this returns
     for (int g = 0; g < G; g++) {
         if (!check_err(g_ctx[g], g_ctx[g]->stream, "decode")) ok = false;
         cudaSetDevice(g_ctx[g]->dev);
@@ -729,7 +735,7 @@ static bool decode_host(const uint8_t* payload, size_t len, int width, int heigh
 }
 
 bool gpu_codec_decode_to_bgr(const uint8_t* payload, size_t len, int width, int height, uint8_t* bmp_rows, int row_stride) {
-    if (row_stride < 3 * width) return fail("decode: row_stride %d < 3*width", row_stride);
+    if (row_stride < 3ll * width) return fail("decode: row_stride %d < 3*width", row_stride);
     return decode_host(payload, len, width, height, bmp_rows, row_stride, 0);
 }
 
