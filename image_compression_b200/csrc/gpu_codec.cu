@@ -758,7 +758,7 @@ bool gpu_codec_decode_to_rgb24(const uint8_t* payload, size_t len, int width, in
 // carries these 512 KB + 256 B until the process exits.
 namespace {
 
-constexpr int NOALLOC_MAX_TILES = 65536;          // 2,097,152 macroblocks, e.g. up to 23168 x 23168 pixels
+constexpr int NOALLOC_MAX_TILES = 2097152 / awi::ENC_TILE_MB;   // 65536 tiles = 2,097,152 macroblocks, e.g. up to 23168 x 23168 pixels
 constexpr size_t NOALLOC_HEADER = 256;            // [0,8) spare, [8,12) tile ticket
 static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_HEADER + (size_t) NOALLOC_MAX_TILES * 8];
 
