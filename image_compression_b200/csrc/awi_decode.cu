@@ -68,6 +68,9 @@ __global__ void __launch_bounds__(256) dec_scan_segments(const uint8_t* __restri
     __shared__ __align__(16) uint8_t s[SEG_STAGE];
     __shared__ uint8_t L[SEG];
     __shared__ unsigned jump[SEG];
+    uint16_t* const cand_list = reinterpret_cast<uint16_t*>(jump);     // positions worth parsing from (dead before the jumps are built)
+    __shared__ int n_cand;
+    if (threadIdx.x == 0) n_cand = 0;
     const unsigned long long seg_start = (unsigned long long) blockIdx.x * SEG;
     if ((reinterpret_cast<uintptr_t>(payload) & 15) == 0 && seg_start + SEG_STAGE <= P) {      // whole stage inside the payload
         static_assert(SEG_STAGE % 16 == 0, "stage is copied in 16-byte pieces");
@@ -80,15 +83,45 @@ __global__ void __launch_bounds__(256) dec_scan_segments(const uint8_t* __restri
         }
     }
     __syncthreads();
+    // A chunk can only start where the one before it ended, and every chunk ends with the 8 zero bits of the
+    // end-of-block symbol (rle.c:106) followed by at most 7 padding bits that the parser skips unread
+    // (bitrw.c:72-76): so the two bytes in front of a chunk start hold 8 consecutive zero bits that end inside
+    // the last one.  Positions without that can never be reached by a parse and are not worth parsing from
+    // (about three in four of them, on photo-like streams); the others are collected and parsed densely.
     for (int p = threadIdx.x; p < SEG; p += 256) {
-        unsigned long long g = seg_start + p;
-        int len = 0;
+        const unsigned long long g = seg_start + p;
+        bool cand = false;
         if (g < P) {
-            len = speculative_len(s + p);
-            if (g + len > P) len = 0;
+            if (g == 0) {
+                cand = true;
+            } else if (g >= 3) {                                         // a chunk is at least 3 bytes
+                const unsigned b1 = p >= 1 ? s[p - 1] : payload[g - 1], b2 = p >= 2 ? s[p - 2] : payload[g - 2];
+                const unsigned z = ~((b2 << 8) | b1) & 0xffffu;          // ones where the stream has zeros
+                unsigned r = z & (z >> 1);
+                r &= r >> 2;
+                r &= r >> 4;                                             // bit i: stream bits i..i+7 of the window are all zero
+                cand = (r & 0xffu) != 0;                                 // the run ends in the last byte (1..8 of its bits)
+            }
         }
+        L[p] = 0;
+        if (g < P && !cand) Lg[g] = 0;
+        const unsigned bal = __ballot_sync(0xffffffffu, cand);
+        if (bal) {
+            const int lane = threadIdx.x & 31;
+            int base = 0;
+            if (lane == 0) base = atomicAdd(&n_cand, __popc(bal));
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (cand) cand_list[base + __popc(bal & ((1u << lane) - 1u))] = (uint16_t) p;
+        }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < n_cand; i += 256) {
+        const int p = cand_list[i];
+        const unsigned long long g = seg_start + p;
+        int len = speculative_len(s + p);
+        if (g + len > P) len = 0;
         L[p] = (uint8_t) len;
-        if (g < P) Lg[g] = (uint8_t) len;
+        Lg[g] = (uint8_t) len;
     }
     __syncthreads();
     // entry offset -> (exit offset into the next segment, chunks passed) for each of the 184 possible entry
@@ -365,6 +398,9 @@ __global__ void __launch_bounds__(REC_THREADS) dec_reconstruct(DecParams P, cons
         if (dc != 0) mask |= 1ull;
         int bit = 12, idx = 1;
         bool bad = my_off < b0 || my_off > b1;
+#ifdef REC_SKIP_PARSE
+        bad = false; if (false)
+#endif
         while (!bad) {
             if (bit + 8 > limit_bits) { bad = true; break; }
             const uint32_t ab = base_bit + (uint32_t) bit;
@@ -401,6 +437,9 @@ __global__ void __launch_bounds__(REC_THREADS) dec_reconstruct(DecParams P, cons
 #pragma unroll
                 for (int x = 0; x < 8; x++) sum[r][x] = 0.0;
             unsigned long long m = S.mask[blk];
+#ifdef REC_SKIP_IDCT
+            m &= 1ull;
+#endif
             const int* cf = S.coef[blk];
             while (m) {
                 const int k = __ffsll((long long) m) - 1;
@@ -458,7 +497,11 @@ __global__ void __launch_bounds__(REC_THREADS) dec_reconstruct(DecParams P, cons
             for (int i = 0; i < 4; i++) {
                 int yy = (yw >> (8 * i)) & 0xff;
                 int cb = (cbw >> (8 * (i >> 1))) & 0xff, cr = (crw >> (8 * (i >> 1))) & 0xff;
+#ifdef REC_SKIP_COLOUR
+                R[i] = yy; G[i] = cb; B[i] = cr;
+#else
                 R[i] = red_of(yy, cr); G[i] = green_of(yy, cb, cr); B[i] = blue_of(yy, cb);
+#endif
             }
             uint8_t* p;
             uint32_t w0, w1, w2;
