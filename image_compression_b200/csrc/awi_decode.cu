@@ -398,9 +398,6 @@ __global__ void __launch_bounds__(REC_THREADS) dec_reconstruct(DecParams P, cons
         if (dc != 0) mask |= 1ull;
         int bit = 12, idx = 1;
         bool bad = my_off < b0 || my_off > b1;
-#ifdef REC_SKIP_PARSE
-        bad = false; if (false)
-#endif
         while (!bad) {
             if (bit + 8 > limit_bits) { bad = true; break; }
             const uint32_t ab = base_bit + (uint32_t) bit;
@@ -437,9 +434,6 @@ __global__ void __launch_bounds__(REC_THREADS) dec_reconstruct(DecParams P, cons
 #pragma unroll
                 for (int x = 0; x < 8; x++) sum[r][x] = 0.0;
             unsigned long long m = S.mask[blk];
-#ifdef REC_SKIP_IDCT
-            m &= 1ull;
-#endif
             const int* cf = S.coef[blk];
             while (m) {
                 const int k = __ffsll((long long) m) - 1;
@@ -494,14 +488,14 @@ __global__ void __launch_bounds__(REC_THREADS) dec_reconstruct(DecParams P, cons
             uint16_t crw = *reinterpret_cast<const uint16_t*>(&S.crp[r >> 1][xl >> 1]);
             int R[4], G[4], B[4];
 #pragma unroll
-            for (int i = 0; i < 4; i++) {
-                int yy = (yw >> (8 * i)) & 0xff;
-                int cb = (cbw >> (8 * (i >> 1))) & 0xff, cr = (crw >> (8 * (i >> 1))) & 0xff;
-#ifdef REC_SKIP_COLOUR
-                R[i] = yy; G[i] = cb; B[i] = cr;
-#else
-                R[i] = red_of(yy, cr); G[i] = green_of(yy, cb, cr); B[i] = blue_of(yy, cb);
-#endif
+            for (int c2 = 0; c2 < 2; c2++) {                      // two chroma samples, two pixels each
+                const int cb = (cbw >> (8 * c2)) & 0xff, cr = (crw >> (8 * c2)) & 0xff;
+                const ChromaTerms t = chroma_terms(cb, cr);
+#pragma unroll
+                for (int i = 2 * c2; i < 2 * c2 + 2; i++) {
+                    const int yy = (yw >> (8 * i)) & 0xff;
+                    R[i] = red_from(yy, t); G[i] = green_from(yy, cb, cr, t); B[i] = blue_from(yy, t);
+                }
             }
             uint8_t* p;
             uint32_t w0, w1, w2;

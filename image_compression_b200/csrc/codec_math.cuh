@@ -166,29 +166,39 @@ AWI_HD int g_exact(int y, int cb, int cr) {
 }
 AWI_HD int b_exact(int y, int cb) { return clamp_trunc(dadd_rn((double) y, dmul_rn(1.772, (double) (cb - 128)))); }
 
-AWI_HD int clamp_div(int n, int d, uint32_t magic, int shift, bool& exact_multiple) {
-    // n / d truncated and clamped to 0..255, branch-free; d in {1000, 125000}.  The multiply-high
-    // quotient is exact for 0 <= n <= 255*d and never too small beyond that, so min(.., 255) clamps.
-    const uint32_t nc = (uint32_t) (n < 0 ? 0 : n);
-    uint32_t q = umulhi32(nc, magic) >> shift;
-    q = q > 255u ? 255u : q;
-    exact_multiple = (nc - q * (uint32_t) d == 0u) && n >= 0;        // includes n == 0 and n == 255*d
-    return (int) q;
+// The chroma part of each channel does not depend on Y, and a (Cb, Cr) sample is shared by the four pixels
+// of its 2x2 cell (color.c:88-105): compute floor(1.402 kr), floor(-0.344136 kb - 0.714136 kr) and
+// floor(1.772 kb) once (kb = Cb-128, kr = Cr-128), then every pixel is an add and a clamp.
+// floor() of the exact rational is what the fp64 expression truncates to, because Y is an integer and the
+// chroma part is either an integer (R, B: only kb/kr = 0, where the expression is exact too) or at least
+// 0.002 (R), 0.004 (B), 8e-6 (G) away from one — except for G when 43017 kb + 89267 kr is a multiple of
+// 125000: there the true value is an integer and rounding decides, so those pixels take the literal expression.
+struct ChromaTerms {
+    int r_add, g_add, b_add;
+    bool g_on_integer;
+};
+AWI_HD ChromaTerms chroma_terms(int cb, int cr) {
+    const int kb = cb - 128, kr = cr - 128;
+    ChromaTerms t;
+    // numerators shifted to be non-negative by a whole number of units, so truncating division is floor;
+    // 4294968 = ceil(2^32/1000) is exact below 6.1e6, 140737489 = ceil(2^44/125000) below 2.1e8
+    t.r_add = (int) umulhi32((uint32_t) (1402 * kr + 180000), 4294968u) - 180;
+    t.b_add = (int) umulhi32((uint32_t) (1772 * kb + 227000), 4294968u) - 227;
+    const uint32_t m = (uint32_t) (17000000 - 43017 * kb - 89267 * kr);      // eighths of 1e-6; |43017 kb + 89267 kr| < 16.94e6
+    const uint32_t q = umulhi32(m, 140737489u) >> 12;
+    t.g_add = (int) q - 136;
+    t.g_on_integer = m - q * 125000u == 0u;
+    return t;
 }
-AWI_HD int red_of(int y, int cr) {
-    bool ex; int v = clamp_div(1000 * y + 1402 * (cr - 128), 1000, 4294968u, 0, ex);
-    return ex ? r_exact(y, cr) : v;
+AWI_HD int clamp255(int v) { return v < 0 ? 0 : (v > 255 ? 255 : v); }
+AWI_HD int red_from(int y, const ChromaTerms& t) { return clamp255(y + t.r_add); }
+AWI_HD int blue_from(int y, const ChromaTerms& t) { return clamp255(y + t.b_add); }
+AWI_HD int green_from(int y, int cb, int cr, const ChromaTerms& t) {
+    return t.g_on_integer ? g_exact(y, cb, cr) : clamp255(y + t.g_add);
 }
-AWI_HD int green_of(int y, int cb, int cr) {
-    // every term of 10^6*y - 344136*(cb-128) - 714136*(cr-128) is a multiple of 8: work in
-    // eighths (divisor 125000); 2^44/125000 -> magic 140737489 is exact for n <= 255*125000.
-    bool ex; int v = clamp_div(125000 * y - 43017 * (cb - 128) - 89267 * (cr - 128), 125000, 140737489u, 12, ex);
-    return ex ? g_exact(y, cb, cr) : v;
-}
-AWI_HD int blue_of(int y, int cb) {
-    bool ex; int v = clamp_div(1000 * y + 1772 * (cb - 128), 1000, 4294968u, 0, ex);
-    return ex ? b_exact(y, cb) : v;
-}
+AWI_HD int red_of(int y, int cr) { return red_from(y, chroma_terms(128, cr)); }
+AWI_HD int green_of(int y, int cb, int cr) { return green_from(y, cb, cr, chroma_terms(cb, cr)); }
+AWI_HD int blue_of(int y, int cb) { return blue_from(y, chroma_terms(cb, 128)); }
 
 // sample (0..255) -> (float)(sample - 128) without an int->float conversion:
 // 0x4B000000 | s is the float 2^23 + s.
