@@ -10,7 +10,7 @@
 //                          possible entry offsets walks the segment: entry -> (exit, #chunks)
 //   2  dec_compose         32-ary tree of those maps (function composition is associative)
 //   3  dec_expand          top-down: true entry offset + first chunk index of every node
-//   4  dec_emit_offsets    per segment: walk from the true entry, write chunk_off[]
+//   4  dec_emit_offsets    per segment (one lane each): walk from the true entry, write chunk_off[]
 //   5  dec_dc_*            per-stream (chunk index mod 6) inclusive scan of the DC diffs
 //   6  dec_reconstruct     8 macroblocks per CTA: parse -> dequantise -> IDCT in the
 //                          reference's exact fp64 operation order (dct.c:64-78, zero terms
@@ -216,23 +216,37 @@ __global__ void dec_root(const unsigned long long* __restrict__ top_table, NodeS
 }
 
 // ---------------------------------------------------------------- 4: offsets
-__global__ void __launch_bounds__(64) dec_emit_offsets(const uint8_t* __restrict__ Lg, unsigned long long P,
-                                                       const NodeState* __restrict__ seg_state,
-                                                       uint32_t* __restrict__ chunk_off, unsigned long long n_chunks) {
-    __shared__ uint8_t L[SEG];
-    const unsigned long long seg_start = (unsigned long long) blockIdx.x * SEG;
+// Walk every segment's chain from its true entry offset and write chunk_off[].  The walk is serial by
+// nature, so a whole warp is spent on 32 of them at once (one segment per lane): the CTA first stages the
+// 32 segments' length bytes in shared memory, then warp 0 walks.
+constexpr int EMIT_SEGS = 32;
+__global__ void __launch_bounds__(256) dec_emit_offsets(const uint8_t* __restrict__ Lg, unsigned long long P,
+                                                        const NodeState* __restrict__ seg_state, long long n_seg,
+                                                        uint32_t* __restrict__ chunk_off, unsigned long long n_chunks) {
+    extern __shared__ __align__(16) uint8_t Ls[];                    // EMIT_SEGS * SEG bytes
+    const long long seg0 = (long long) blockIdx.x * EMIT_SEGS;
+    const unsigned long long byte0 = (unsigned long long) seg0 * SEG;
+    const unsigned long long span = min((unsigned long long) EMIT_SEGS * SEG, P - byte0);   // Lg holds P (+16 spare) bytes
+    {
+        const uint4* src = reinterpret_cast<const uint4*>(Lg + byte0);                  // byte0 is a multiple of SEG, Lg 256-aligned
+        const int n16 = (int) ((span + 15) >> 4);
+        for (int i = threadIdx.x; i < n16; i += 256) reinterpret_cast<uint4*>(Ls)[i] = __ldg(src + i);
+    }
+    __syncthreads();
+    if (threadIdx.x >= 32) return;
+    const long long seg = seg0 + threadIdx.x;
+    if (seg >= n_seg) return;
+    const NodeState st = seg_state[seg];
+    if (!st.ok) return;
+    const unsigned long long seg_start = (unsigned long long) seg * SEG;
     const long long remain = (long long) (P - seg_start);
     const int lim = remain < SEG ? (int) remain : SEG;
-    for (int i = threadIdx.x; i < lim; i += 64) L[i] = Lg[seg_start + i];
-    __syncthreads();
-    if (threadIdx.x != 0) return;
-    NodeState st = seg_state[blockIdx.x];
-    if (!st.ok) return;
+    const uint8_t* L = Ls + threadIdx.x * SEG;
     int pos = st.entry;
     unsigned long long c = st.first_chunk;
     while (pos < lim && c < n_chunks) {
         chunk_off[c++] = (uint32_t) (seg_start + pos);
-        int l = L[pos];
+        const int l = L[pos];
         if (l == 0) break;
         pos += l;
     }
@@ -571,6 +585,17 @@ cudaError_t launch_decode(const DecParams& P, void* workspace, size_t workspace_
     const long long n_chunks = n_mb * 6;
     DecLayout Lo = dec_layout(P.payload_len, n_chunks);
     if (workspace_bytes < Lo.total) return cudaErrorInvalidValue;
+    {   // kernels with more than 48 KB of dynamic shared memory have to opt in, once per device
+        static bool attr_set[64] = { false };
+        int dev = 0;
+        cudaGetDevice(&dev);
+        if (dev < 0 || dev >= 64 || !attr_set[dev]) {
+            cudaError_t e = cudaFuncSetAttribute(dec_reconstruct, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sizeof(RecSmem));
+            if (e == cudaSuccess) e = cudaFuncSetAttribute(dec_emit_offsets, cudaFuncAttributeMaxDynamicSharedMemorySize, EMIT_SEGS * SEG);
+            if (e != cudaSuccess) return e;
+            if (dev >= 0 && dev < 64) attr_set[dev] = true;
+        }
+    }
     uint8_t* ws = static_cast<uint8_t*>(workspace);
     uint32_t* chunk_off = reinterpret_cast<uint32_t*>(ws + Lo.off_chunk_off);
 
@@ -593,8 +618,8 @@ cudaError_t launch_decode(const DecParams& P, void* workspace, size_t workspace_
             const long long nc = Lo.n_node[lv - 1];
             dec_expand<<<(unsigned) ((nc + 127) / 128), 128, 0, stream>>>(pre(lv), nc, state(lv), state(lv - 1));
         }
-        dec_emit_offsets<<<(unsigned) Lo.n_seg, 64, 0, stream>>>(Lg, P.payload_len, state(0), chunk_off,
-                                                                (unsigned long long) n_chunks);
+        dec_emit_offsets<<<(unsigned) ((Lo.n_seg + EMIT_SEGS - 1) / EMIT_SEGS), 256, EMIT_SEGS * SEG, stream>>>(
+            Lg, P.payload_len, state(0), Lo.n_seg, chunk_off, (unsigned long long) n_chunks);
     } else {
         cudaError_t e = cudaMemcpyAsync(chunk_off, chunk_off_in, (size_t) n_chunks * 4, cudaMemcpyDeviceToDevice, stream);
         if (e != cudaSuccess) return e;
@@ -609,14 +634,6 @@ cudaError_t launch_decode(const DecParams& P, void* workspace, size_t workspace_
     dec_dc_tile<1><<<(unsigned) Lo.n_dct, DCT_MB, 0, stream>>>(P.payload, chunk_off, n_mb, nullptr, tile_base, dcabs, P.payload_len, err);
     }
 
-    static bool attr_set[64] = { false };
-    int dev = 0;
-    cudaGetDevice(&dev);
-    if (dev < 64 && !attr_set[dev]) {
-        cudaError_t e = cudaFuncSetAttribute(dec_reconstruct, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sizeof(RecSmem));
-        if (e != cudaSuccess) return e;
-        attr_set[dev] = true;
-    }
     const int tiles_per_row = (P.mbw + REC_MB - 1) / REC_MB;
     const int rows = P.mb_row1 - P.mb_row0;
     if (rows > 0)
