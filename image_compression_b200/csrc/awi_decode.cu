@@ -66,18 +66,20 @@ __device__ __forceinline__ int speculative_len(const uint8_t* s) {
 __global__ void __launch_bounds__(256) dec_scan_segments(const uint8_t* __restrict__ payload, unsigned long long P,
                                                          uint8_t* __restrict__ Lg, unsigned long long* __restrict__ table) {
     __shared__ __align__(16) uint8_t s[SEG_STAGE];
-    __shared__ uint8_t L[SEG];
-    __shared__ unsigned jump[SEG];
-    uint16_t* const cand_list = reinterpret_cast<uint16_t*>(jump);     // positions worth parsing from (dead before the jumps are built)
-    __shared__ int n_cand;
-    if (threadIdx.x == 0) n_cand = 0;
+    __shared__ uint16_t idx[SEG];            // position -> index in the candidate list (NONE: not a candidate)
+    __shared__ uint16_t cand_pos[SEG];       // candidate list, ascending positions
+    __shared__ uint8_t cand_len[SEG];        // chunk length parsed from each candidate (0: no legal chunk there)
+    __shared__ unsigned jump[SEG];           // per candidate: (where its chain has got to, chunks counted)
+    __shared__ int warp_cnt[8];
+    constexpr unsigned NONE = 0xffffu, DEAD = 0xffffu, EXITED = 0x8000u;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const unsigned long long seg_start = (unsigned long long) blockIdx.x * SEG;
     if ((reinterpret_cast<uintptr_t>(payload) & 15) == 0 && seg_start + SEG_STAGE <= P) {      // whole stage inside the payload
         static_assert(SEG_STAGE % 16 == 0, "stage is copied in 16-byte pieces");
         const uint4* src = reinterpret_cast<const uint4*>(payload + seg_start);
-        for (int i = threadIdx.x; i < SEG_STAGE / 16; i += 256) reinterpret_cast<uint4*>(s)[i] = __ldg(src + i);
+        for (int i = tid; i < SEG_STAGE / 16; i += 256) reinterpret_cast<uint4*>(s)[i] = __ldg(src + i);
     } else {
-        for (int i = threadIdx.x; i < SEG_STAGE; i += 256) {
+        for (int i = tid; i < SEG_STAGE; i += 256) {
             unsigned long long g = seg_start + i;
             s[i] = g < P ? payload[g] : 0;
         }
@@ -86,83 +88,108 @@ __global__ void __launch_bounds__(256) dec_scan_segments(const uint8_t* __restri
     // A chunk can only start where the one before it ended, and every chunk ends with the 8 zero bits of the
     // end-of-block symbol (rle.c:106) followed by at most 7 padding bits that the parser skips unread
     // (bitrw.c:72-76): so the two bytes in front of a chunk start hold 8 consecutive zero bits that end inside
-    // the last one.  Positions without that can never be reached by a parse and are not worth parsing from
-    // (about three in four of them, on photo-like streams); the others are collected and parsed densely.
-    for (int p = threadIdx.x; p < SEG; p += 256) {
-        const unsigned long long g = seg_start + p;
-        bool cand = false;
-        if (g < P) {
-            if (g == 0) {
-                cand = true;
-            } else if (g >= 3) {                                         // a chunk is at least 3 bytes
-                const unsigned b1 = p >= 1 ? s[p - 1] : payload[g - 1], b2 = p >= 2 ? s[p - 2] : payload[g - 2];
-                const unsigned z = ~((b2 << 8) | b1) & 0xffffu;          // ones where the stream has zeros
-                unsigned r = z & (z >> 1);
-                r &= r >> 2;
-                r &= r >> 4;                                             // bit i: stream bits i..i+7 of the window are all zero
-                cand = (r & 0xffu) != 0;                                 // the run ends in the last byte (1..8 of its bits)
+    // the last one.  Positions without that can never be reached by a parse (about two in three on photo-like
+    // streams, four in five on noise); the others are collected, in order, and everything after this works on
+    // that list.  Thread t looks at positions 8t .. 8t+7.
+    unsigned flags = 0;
+    {
+        const int p0 = 8 * tid;
+        unsigned b2 = 0, b1 = 0;                                         // the two bytes in front of position p
+        if (p0 >= 2) { b2 = s[p0 - 2]; b1 = s[p0 - 1]; }
+        else if (seg_start >= 2) { b2 = payload[seg_start - 2]; b1 = payload[seg_start - 1]; }      // thread 0 of a later segment
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            const unsigned long long g = seg_start + p0 + k;
+            bool cand = false;
+            if (g < P) {
+                if (g == 0) {
+                    cand = true;
+                } else if (g >= 3) {                                     // a chunk is at least 3 bytes
+                    const unsigned z = ~((b2 << 8) | b1) & 0xffffu;      // ones where the stream has zeros
+                    unsigned r = z & (z >> 1);
+                    r &= r >> 2;
+                    r &= r >> 4;                                         // bit i: window bits i..i+7 are all zero
+                    cand = (r & 0xffu) != 0;                             // the run ends inside the last byte
+                }
+                if (!cand) Lg[g] = 0;
             }
+            flags |= (cand ? 1u : 0u) << k;
+            b2 = b1;
+            b1 = s[p0 + k];
         }
-        L[p] = 0;
-        if (g < P && !cand) Lg[g] = 0;
-        const unsigned bal = __ballot_sync(0xffffffffu, cand);
-        if (bal) {
-            const int lane = threadIdx.x & 31;
-            int base = 0;
-            if (lane == 0) base = atomicAdd(&n_cand, __popc(bal));
-            base = __shfl_sync(0xffffffffu, base, 0);
-            if (cand) cand_list[base + __popc(bal & ((1u << lane) - 1u))] = (uint16_t) p;
+    }
+    int n_cand;
+    {
+        const int mine = __popc(flags);
+        int incl = mine;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += t;
+        }
+        if (lane == 31) warp_cnt[warp] = incl;
+        __syncthreads();
+        int base = 0, total = 0;
+#pragma unroll
+        for (int w = 0; w < 8; w++) { const int t = warp_cnt[w]; if (w < warp) base += t; total += t; }
+        n_cand = total;
+        int at = base + incl - mine;
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            const bool cand = (flags >> k) & 1u;
+            idx[8 * tid + k] = cand ? (uint16_t) at : (uint16_t) NONE;
+            if (cand) cand_pos[at++] = (uint16_t) (8 * tid + k);
         }
     }
     __syncthreads();
-    for (int i = threadIdx.x; i < n_cand; i += 256) {
-        const int p = cand_list[i];
+    for (int i = tid; i < n_cand; i += 256) {
+        const int p = cand_pos[i];
         const unsigned long long g = seg_start + p;
         int len = speculative_len(s + p);
         if (g + len > P) len = 0;
-        L[p] = (uint8_t) len;
+        cand_len[i] = (uint8_t) len;
         Lg[g] = (uint8_t) len;
     }
     __syncthreads();
     // entry offset -> (exit offset into the next segment, chunks passed) for each of the 184 possible entry
-    // offsets, by pointer jumping over jump[p] = (where the chain from p has got to, chunks counted), one
-    // 32-bit word per position so a pair is always read consistently; 10 doublings cover the longest
-    // chain (2048/3 chunks).  In-place updates may see a neighbour's old or new word: both are valid jumps.
+    // offsets, by pointer jumping over the candidates: jump[i] = (where the chain from candidate i has got to,
+    // chunks counted), one 32-bit word each so a pair is always read consistently; 10 doublings cover the
+    // longest chain (2048/3 chunks).  In-place updates may see a neighbour's old or new word: both are valid jumps.
     const long long remain = (long long) (P - seg_start);           // bytes of payload from seg_start on
     const int lim = remain < SEG ? (int) remain : SEG;              // in the last segment a legal chain ends exactly at lim
-    constexpr unsigned DEAD = 0xffffu;
-    for (int p = threadIdx.x; p < SEG; p += 256) {
+    for (int i = tid; i < n_cand; i += 256) {
         unsigned w = DEAD;
-        const int l = L[p];
+        const int l = cand_len[i], p = cand_pos[i];
         if (l != 0 && p < lim) {
             const int q = p + l;                                     // q <= lim in the last segment (longer chunks were zeroed)
-            w = (q < lim ? (unsigned) q : (unsigned) (SEG + (q - lim))) | (1u << 16);
+            const unsigned to = q < lim ? (unsigned) idx[q] : EXITED + (unsigned) (q - lim);      // NONE == DEAD: the chain stops at q
+            w = to == DEAD ? DEAD : (to | (1u << 16));
         }
-        jump[p] = w;
+        jump[i] = w;
     }
     __syncthreads();
     for (int round = 0; round < 10; round++) {
         int moved = 0;
-        for (int p = threadIdx.x; p < SEG; p += 256) {
-            const unsigned w = jump[p], n = w & 0xffffu;
-            if (n < (unsigned) SEG) {
+        for (int i = tid; i < n_cand; i += 256) {
+            const unsigned w = jump[i], n = w & 0xffffu;
+            if (n < EXITED) {
                 const unsigned w2 = jump[n], n2 = w2 & 0xffffu;
-                jump[p] = n2 == DEAD ? DEAD : (n2 | ((w >> 16) + (w2 >> 16)) << 16);
+                jump[i] = n2 == DEAD ? DEAD : (n2 | ((w >> 16) + (w2 >> 16)) << 16);
                 moved = 1;
             }
         }
         if (!__syncthreads_or(moved)) break;                         // every chain has left the segment (or died)
     }
-    if (threadIdx.x < MAXCH) {
-        const int e = threadIdx.x;
+    if (tid < MAXCH) {
+        const int e = tid;
         unsigned long long r = 0ull;
         if (e == lim) {
             r = ent_make(0, 0);                                      // entering exactly at the payload end: nothing left
-        } else if (e < lim) {
-            const unsigned w = jump[e], n = w & 0xffffu;
-            if (n != DEAD && n >= (unsigned) SEG) r = ent_make(w >> 16, remain <= SEG ? 0 : (int) (n - SEG));
+        } else if (e < lim && idx[e] != NONE) {
+            const unsigned w = jump[idx[e]], n = w & 0xffffu;
+            if (n != DEAD && n >= EXITED) r = ent_make(w >> 16, remain <= SEG ? 0 : (int) (n - EXITED));
         }
-        table[(unsigned long long) blockIdx.x * MAXCH + threadIdx.x] = r;
+        table[(unsigned long long) blockIdx.x * MAXCH + tid] = r;
     }
 }
 
