@@ -62,6 +62,7 @@ struct __align__(16) EncSmem {
     uint16_t amb_list[THREADS];                  // chunks with flagged coefficients
     int amb_count;
     unsigned long long tile_base;
+    unsigned long long load_bar;                 // mbarrier the bulk copies of phase A complete on
     int tile;
 };
 
@@ -88,6 +89,28 @@ __device__ __forceinline__ uint4 ld_stream(const uint4* p) {
     asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
     return v;
 }
+// Bulk asynchronous copies (the TMA unit, no tensor map needed for a contiguous run): one elected lane per
+// image row asks for 1536 bytes global -> shared; the bytes are counted on an mbarrier.
+__device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t) __cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, uint32_t arrivals) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_addr(bar)), "r"(arrivals) : "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");       // the copy engine must see the initialised barrier
+}
+__device__ __forceinline__ void mbar_arrive_expect(unsigned long long* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_load(void* dst, const void* src, uint32_t bytes, unsigned long long* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_addr(dst)), "l"(src), "r"(bytes), "r"(smem_addr(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, uint32_t parity) {
+    uint32_t done;
+    do {
+        asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
+                     : "=r"(done) : "r"(smem_addr(bar)), "r"(parity) : "memory");
+    } while (!done);
+}
+
 // bmp.c:48-119 addressing.  Pixel bytes outside the image read as zero (bmp.c:89-93,106-109).
 // `src` points at the piece; `valid` = bytes of it inside the image row (<= 0: none).
 __device__ __forceinline__ uint4 load_piece(const uint8_t* src, int valid, int align) {
@@ -288,22 +311,39 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
     const int n_mb = min(TILE_MB, P.mb1 - mb_first);
     const bool has_halo = mb_first > 0;
 
-    // ---- A: stage pixels.  Thread = one 16-byte piece column (macroblock m, piece k) x 8 rows.
+    // ---- A: stage pixels.  Common case (a full tile inside one macroblock row and inside the image, 16-byte
+    //      aligned rows): 16 bulk copies of 1536 contiguous bytes, issued by 16 lanes of warp 0, land in the
+    //      padded rows of S.raw on their own; nothing passes through registers.  Otherwise thread = one
+    //      16-byte piece column (macroblock m, piece k) x 8 rows, with edge handling.
     {
         const uint8_t* const rows = P.rows + (long long) frame * P.frame_stride;
+        const int my_first = mb_first / P.mbw, mx_first = mb_first - my_first * P.mbw;
+        const bool bulk = P.align == 16 && n_mb == TILE_MB && mx_first + TILE_MB <= P.mbw &&
+                          (mx_first + TILE_MB) * 16 <= P.width && my_first * 16 + 16 <= P.height;
+        if (bulk && warp == 0) {
+            if (lane == 0) {
+                mbar_init(&S.load_bar, 1);
+                mbar_arrive_expect(&S.load_bar, 16u * TILE_MB * 48u);
+            }
+            __syncwarp();
+            if (lane < 16) {
+                const uint8_t* src = rows + (long long) (P.height - 1 - (my_first * 16 + lane)) * P.stride + mx_first * 48;
+                bulk_load(S.raw + lane * PITCH, src, TILE_MB * 48, &S.load_bar);
+            }
+        }
         const int col = tid % (3 * TILE_MB), m = col / 3, k = col - 3 * m;
         const int r0 = tid / (3 * TILE_MB);                       // 0 or 1
         uint4 v[8];
 #pragma unroll
         for (int i = 0; i < 8; i++) v[i] = make_uint4(0, 0, 0, 0);
-        if (m < n_mb) {
+        if (!bulk && m < n_mb) {
             const int g = mb_first + m;
             const int my = g / P.mbw, mx = g - my * P.mbw;
             const int xb = mx * 48 + k * 16;
             const int valid = P.width * 3 - xb;
             const int y0 = my * 16 + r0;
             const uint8_t* src = rows + (long long) (P.height - 1 - y0) * P.stride + xb;
-            if (P.align == 16 && valid >= 16 && y0 + 14 < P.height) {     // the common case: 8 plain 128-bit loads
+            if (P.align == 16 && valid >= 16 && y0 + 14 < P.height) {     // 8 plain 128-bit loads
 #pragma unroll
                 for (int i = 0; i < 8; i++) v[i] = ld_stream(reinterpret_cast<const uint4*>(src - (long long) (2 * i) * P.stride));
             } else {
@@ -321,10 +361,13 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
             if (y < P.height)
                 h = load_piece(rows + (long long) (P.height - 1 - y) * P.stride + xb, P.width * 3 - xb, P.align);
         }
-        uint8_t* dst = S.raw + r0 * PITCH + col * 16;
+        if (!bulk) {
+            uint8_t* dst = S.raw + r0 * PITCH + col * 16;
 #pragma unroll
-        for (int i = 0; i < 8; i++) *reinterpret_cast<uint4*>(dst + i * 2 * PITCH) = v[i];
+            for (int i = 0; i < 8; i++) *reinterpret_cast<uint4*>(dst + i * 2 * PITCH) = v[i];
+        }
         if (tid < 48) reinterpret_cast<uint4*>(S.halo)[tid] = h;
+        if (bulk && warp == 0) mbar_wait(&S.load_bar, 0);          // the barrier below passes the bytes on to the other warps
     }
     PHASE_MARK(0);
     __syncthreads();
