@@ -248,6 +248,8 @@ bool encode_dev_impl(Ctx* c, const uint8_t* d_rows, int width, int height, long 
     P.width = width;
     P.height = height;
     P.align = align_of(d_rows, stride);
+    if (n_frames > 1 && frame_stride % P.align != 0)         // every frame's rows must be as aligned as the first one's
+        P.align = frame_stride % 4 == 0 && P.align >= 4 ? 4 : 1;
     P.mbw = mbw;
     P.mb0 = r0 * mbw;
     P.mb1 = r1 * mbw;

@@ -206,10 +206,11 @@ def test_sample1_if_present(gpu, golden):
 def test_batch_dev_one_launch(gpu, port):
     """gpu_codec_encode_batch_bgr_dev: frames in one launch, predictors restart per frame."""
     import torch
-    for w, h, n in ((192, 108, 7), (528, 48, 3), (37, 21, 5)):
+    # the last two cases: frames 4 and 1 bytes off the 16-byte grid (the loader must drop to narrower loads)
+    for w, h, n, skew in ((192, 108, 7, 0), (528, 48, 3, 0), (37, 21, 5, 0), (528, 48, 3, 4), (192, 108, 4, 1)):
         stride = synth.bmp_stride(w)
         frames = [synth.frame_bgr_bottomup("photo" if f % 2 else "noise", w, h, 0xA11CE04, f).reshape(-1) for f in range(n)]
-        fs = ((stride * h + 255) // 256) * 256
+        fs = ((stride * h + 255) // 256) * 256 + skew
         buf = torch.zeros(n * fs, dtype=torch.uint8, device="cuda")
         for f in range(n):
             buf[f * fs: f * fs + stride * h] = torch.from_numpy(frames[f]).cuda()
