@@ -197,18 +197,24 @@ __global__ void __launch_bounds__(256) dec_scan_segments(const uint8_t* __restri
 // out[i][e] = children c0..c1 of node i applied in turn to entry e.  On the way, pre[c][e] records the state
 // in front of child c (entry offset into it, chunks counted before it) so that the top-down pass needs one
 // look-up per child instead of a chain of them.
+// The chain through the children is a pointer chase; the children's tables are fetched into shared memory
+// first (independent, coalesced loads) so that the 32 dependent steps cost shared-memory latency, not DRAM's.
 __global__ void __launch_bounds__(192) dec_compose(const unsigned long long* __restrict__ in, long long n_in,
                                                    unsigned long long* __restrict__ out,
                                                    unsigned long long* __restrict__ pre) {
+    extern __shared__ unsigned long long child_tab[];               // FAN * MAXCH entries
+    const long long c0 = (long long) blockIdx.x * FAN, c1 = c0 + FAN < n_in ? c0 + FAN : n_in;
+    const int n = (int) (c1 - c0);
+    for (int i = threadIdx.x; i < n * MAXCH; i += 192) child_tab[i] = in[c0 * MAXCH + i];
+    __syncthreads();
     if (threadIdx.x >= MAXCH) return;
-    long long c0 = (long long) blockIdx.x * FAN, c1 = c0 + FAN < n_in ? c0 + FAN : n_in;
     int e = threadIdx.x;
     unsigned long long cnt = 0;
     bool ok = true;
-    for (long long c = c0; c < c1; c++) {
-        pre[c * MAXCH + threadIdx.x] = ok ? ent_make(cnt, e) : 0ull;
+    for (int c = 0; c < n; c++) {
+        pre[(c0 + c) * MAXCH + threadIdx.x] = ok ? ent_make(cnt, e) : 0ull;
         if (ok) {
-            unsigned long long t = in[c * MAXCH + e];
+            unsigned long long t = child_tab[c * MAXCH + e];
             if (!(t & ENT_OK)) ok = false;
             else { cnt += ent_cnt(t); e = ent_exit(t); }
         }
@@ -329,24 +335,48 @@ __global__ void __launch_bounds__(DCT_MB) dec_dc_tile(const uint8_t* __restrict_
     }
 }
 
-// exclusive scan of the tile sums (one CTA; tiles <= a few thousand)
+// exclusive scan of the tile sums (one CTA; each thread owns a contiguous run of tiles, the 1024 partial
+// sums are scanned with shuffles)
 __global__ void __launch_bounds__(1024) dec_dc_scan_tiles(const int* __restrict__ tile_sum, long long n_tiles,
                                                           int* __restrict__ tile_base) {
-    __shared__ int part[1024][6];
+    __shared__ int wtot[32][6];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const long long per = (n_tiles + 1023) / 1024;
-    const long long t0 = (long long) threadIdx.x * per, t1 = t0 + per < n_tiles ? t0 + per : n_tiles;
+    const long long t0 = min((long long) threadIdx.x * per, n_tiles), t1 = t0 + per < n_tiles ? t0 + per : n_tiles;
     int s[6] = { 0, 0, 0, 0, 0, 0 };
     for (long long t = t0; t < t1; t++)
+#pragma unroll
         for (int k = 0; k < 6; k++) s[k] += tile_sum[t * 6 + k];
-    for (int k = 0; k < 6; k++) part[threadIdx.x][k] = s[k];
-    __syncthreads();
-    if (threadIdx.x < 6) {                       // 1024 serial adds per component: negligible
-        int run = 0;
-        for (int i = 0; i < 1024; i++) { int t = part[i][threadIdx.x]; part[i][threadIdx.x] = run; run += t; }
+    int incl[6];
+#pragma unroll
+    for (int k = 0; k < 6; k++) {
+        incl[k] = s[k];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, incl[k], o);
+            if (lane >= o) incl[k] += t;
+        }
+        if (lane == 31) wtot[warp][k] = incl[k];
     }
     __syncthreads();
-    for (int k = 0; k < 6; k++) s[k] = part[threadIdx.x][k];
+    if (warp == 0) {
+#pragma unroll
+        for (int k = 0; k < 6; k++) {
+            const int w = wtot[lane][k];
+            int wi = w;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int t = __shfl_up_sync(0xffffffffu, wi, o);
+                if (lane >= o) wi += t;
+            }
+            wtot[lane][k] = wi - w;                       // exclusive over warps
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < 6; k++) s[k] = wtot[warp][k] + incl[k] - s[k];          // exclusive prefix of my run
     for (long long t = t0; t < t1; t++)
+#pragma unroll
         for (int k = 0; k < 6; k++) { tile_base[t * 6 + k] = s[k]; s[k] += tile_sum[t * 6 + k]; }
 }
 
@@ -639,7 +669,7 @@ cudaError_t launch_decode(const DecParams& P, void* workspace, size_t workspace_
         dec_scan_segments<<<(unsigned) Lo.n_seg, 256, 0, stream>>>(P.payload, P.payload_len, Lg, table(0));
         auto pre = [&](int lv) { return reinterpret_cast<unsigned long long*>(ws + Lo.off_pre[lv]); };
         for (int lv = 1; lv < Lo.levels; lv++)
-            dec_compose<<<(unsigned) Lo.n_node[lv], 192, 0, stream>>>(table(lv - 1), Lo.n_node[lv - 1], table(lv), pre(lv));
+            dec_compose<<<(unsigned) Lo.n_node[lv], 192, FAN * MAXCH * 8, stream>>>(table(lv - 1), Lo.n_node[lv - 1], table(lv), pre(lv));
         dec_root<<<1, 32, 0, stream>>>(table(Lo.levels - 1), state(Lo.levels - 1), (unsigned long long) n_chunks, err);
         for (int lv = Lo.levels - 1; lv >= 1; lv--) {
             const long long nc = Lo.n_node[lv - 1];

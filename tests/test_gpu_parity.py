@@ -146,6 +146,51 @@ def test_decode_modes_agree(gpu, port):
         assert dst.cpu().numpy().tobytes() == want.tobytes()
 
 
+def _chunk_bits(p: np.ndarray, start: int) -> int:
+    """Bits of the chunk starting at byte `start`, up to and including its end-of-block symbol (rle.c:113-167)."""
+    def sym(bit):
+        b = start * 8 + bit
+        v = (int(p[b >> 3]) << 8) | (int(p[(b >> 3) + 1]) if (b >> 3) + 1 < p.size else 0)
+        return (v >> (8 - (b & 7))) & 0xFF
+    bit = 12
+    while True:
+        s8 = sym(bit)
+        if s8 == 0:
+            return bit + 8
+        bit += 8 + (s8 & 15)
+
+
+def test_padding_bits_are_ignored_like_the_reference(gpu, port):
+    """bitrw.c:72-76 drops the partial byte after a chunk without looking at it.  Streams whose padding bits
+    are not zero (no encoder of the reference writes them, its decoder accepts them) must decode the same,
+    also through the stand-alone boundary discovery, whose candidate test may rely only on the end-of-block zeros."""
+    import torch
+    rng = np.random.default_rng(11)
+    for kind, w, h in (("photo", 320, 208), ("noise", 144, 80), ("flat", 96, 64)):
+        stride = synth.bmp_stride(w)
+        rows = synth.frame_bgr_bottomup(kind, w, h, 0xA11CE06)
+        p, _, lens = port.encode_bgr(rows, w, h, stride, want_coefs=True)
+        p = np.array(p, dtype=np.uint8)
+        starts = np.concatenate([[0], np.cumsum(lens)[:-1]]).astype(np.int64)
+        want, used = port.decode(p, w, h)
+        dirty = p.copy()
+        touched = 0
+        for st, ln in zip(starts, lens):
+            pad = int(ln) * 8 - _chunk_bits(p, int(st))
+            assert 0 <= pad <= 7
+            if pad:
+                dirty[st + ln - 1] |= int(rng.integers(0, 1 << pad))
+                touched += 1
+        assert touched > len(lens) // 2 and (dirty != p).any()
+        got_ref, used2 = port.decode(dirty, w, h)
+        assert used2 == used and got_ref.tobytes() == want.tobytes()          # the oracle (= reference) does not care
+        dst = torch.zeros(stride * h, dtype=torch.uint8, device="cuda")
+        gpu.decode_dev(0, torch.from_numpy(dirty).cuda(), dirty.size, w, h, dst, stride)
+        gpu.sync_check(0)
+        assert dst.cpu().numpy().tobytes() == want.tobytes(), kind
+        assert np.asarray(gpu.decode_to_bgr(dirty, w, h)).tobytes()[: want.size] == want.tobytes()
+
+
 def test_malformed_streams_are_rejected(gpu):
     from image_compression_b200 import codec
     w, h = 64, 32
