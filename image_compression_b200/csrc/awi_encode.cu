@@ -56,8 +56,6 @@ struct __align__(16) EncSmem {
     unsigned long long amb[THREADS];             // per chunk: natural positions to recompute
     int dc[(TILE_MB + 1) * 6];                   // quantised DCs, [0] = halo macroblock
     int halo_sum[6];
-    uint32_t len[THREADS];                       // chunk byte lengths, chunk order
-    uint32_t off[THREADS];                       // exclusive offsets inside the tile
     uint32_t warp_tot[NWARPS];
     uint16_t amb_list[THREADS];                  // chunks with flagged coefficients
     int amb_count;
