@@ -6,24 +6,27 @@
 // and the bit-serial writer underneath it (bitrw.c:9-43):
 //
 //   tile = 32 consecutive macroblocks (raster order), one CTA of 6 warps
-//   A  coalesced 128-bit loads of the tile's 16 pixel rows (bottom-up BGR) -> smem
+//   A  the tile's 16 pixel rows (bottom-up BGR) -> smem: 16 bulk asynchronous copies (TMA,
+//      mbarrier completion) for full interior tiles, coalesced 128-bit loads with edge
+//      handling otherwise
 //   B  8 lanes per 8x8 block (one image row each, then one column each): colour ->
-//      AAN row pass in registers -> 8x8 transpose through padded smem -> AAN column
+//      AAN row pass in registers -> 8x8 transpose through smem -> AAN column
 //      pass -> quantise (+ambiguity flags) with per-lane constants held in registers
 //      -> scan-order int8 coefficients in smem;  exact DC;  halo macroblock DCs.
-//      A warp walks 32 blocks in 8 iterations of a short loop (small instruction
-//      footprint, ~60 registers: 4-5 CTAs per SM).
+//      The tile's 48 iterations (4 blocks each) are dealt round-robin to the warps.
 //   C  flagged coefficients recomputed warp-cooperatively in the reference's exact
 //      operation order
 //   D  one thread per chunk: run-length symbols + bit packing into a smem slot
-//   E  CTA scan of chunk byte lengths; warp 0 resolves the tile's payload offset by
-//      decoupled look-back (128 descriptors per round) while the others compact
-//   F  coalesced word copy of the compacted tile to its final payload offset
+//   E  CTA scan of chunk byte lengths, chunks compacted in smem
+//   F  two-pass mode (regular): the tile goes to a staging buffer in completion order;
+//      enc_scan_tiles + enc_gather_tiles place the tiles afterwards.
+//      single-pass mode (no-alloc entry point): warp 0 resolves the tile's payload offset
+//      by decoupled look-back (128 descriptors per round), coalesced word copy to it.
 //
 // Chunks are byte aligned (rle.c:107) so the device-wide scan is over BYTE lengths.
 // The only cross-tile state, the six DC predictors (awi.c:91-92), is rebuilt from a
 // one-macroblock halo with the integer DC formula, so tiles (and stripes on other
-// GPUs) never wait on each other for data — only for the output offset.
+// GPUs) never wait on each other for data — and in two-pass mode not for the output offset either.
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include "codec_math.cuh"
