@@ -33,6 +33,10 @@ for sec in sections[:1] if want is None else [s for s in sections if want in s["
     print("%-10s %14s %7s %9s" % ("opcode", "executed", "share", "samples%"))
     for op, c in ops.most_common(28):
         print("%-10s %14d %6.1f%% %8.1f%%" % (op, c, 100 * c / tot, 100 * smp[op] / max(ts, 1)))
+    print("async-copy / barrier opcodes (TMA evidence):")
+    for r in data:
+        if any(t in r[iS] for t in ("UBLKCP", "UTMALDG", "UTMASTG", "SYNCS", "UTCMMA", "TCGEN")) and int(r[iE]) > 0:
+            print("  %10s  %s" % (r[iE], r[iS].strip()[:110]))
     print("stall samples:")
     for name in hdr:
         if name.startswith("stall_") and "Not Issued" not in name:
