@@ -41,6 +41,7 @@ bool fail(const char* fmt, ...) {
 
 constexpr int MAX_SUB = 32;               // sub-stripes a frame is cut into to overlap PCIe copies with the kernels
 constexpr size_t SUB_BYTES = 48u << 20;   // aim for ~48 MB of pixels per sub-stripe
+constexpr size_t SUB_BYTES_MIN = 4u << 20;
 constexpr size_t ENC_WS_HEADER = 256;     // [0,8) payload length, [8,12) tile ticket, [16,20) staging cursor
 
 struct Buf {
@@ -481,7 +482,12 @@ static bool encode_stripe_async(Ctx* c, const uint8_t* bmp_rows, int width, int 
     const size_t cap = (size_t) (R1 - R0) * mbw * 6 * 121 + 16;
     CU(cudaSetDevice(c->dev));
     if (!ensure(c->in, in_bytes) || !ensure(c->out, cap)) return false;
-    int n_sub = (int) ((in_bytes + SUB_BYTES - 1) / SUB_BYTES);
+    // ~48 MB per sub-stripe for large frames; smaller frames are still cut in about eight (not below 4 MB a piece)
+    // so that most of their encode time hides behind the upload too
+    size_t sub_bytes = in_bytes / 8;
+    if (sub_bytes > SUB_BYTES) sub_bytes = SUB_BYTES;
+    if (sub_bytes < SUB_BYTES_MIN) sub_bytes = SUB_BYTES_MIN;
+    int n_sub = (int) ((in_bytes + sub_bytes - 1) / sub_bytes);
     if (n_sub > MAX_SUB) n_sub = MAX_SUB;
     if (n_sub > R1 - R0) n_sub = R1 - R0;
     if (n_sub < 1) n_sub = 1;
