@@ -309,9 +309,11 @@ bool decode_dev_impl(Ctx* c, const uint8_t* d_payload, size_t len, int width, in
 
 bool check_err(Ctx* c, cudaStream_t st, const char* what) {
     CU(cudaSetDevice(c->dev));
+    // the flags ride home behind whatever is queued on the stream: one wait instead of a wait and a blocking copy
+    volatile unsigned int* h_err = reinterpret_cast<volatile unsigned int*>(c->h_len + 4);
+    CU(cudaMemcpyAsync(const_cast<unsigned int*>(h_err), c->d_err, 4, cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
-    unsigned int e = 0;
-    CU(cudaMemcpy(&e, c->d_err, 4, cudaMemcpyDeviceToHost));
+    const unsigned int e = *h_err;
     if (e) {
         CU(cudaMemset(c->d_err, 0, 4));
         return fail("%s: device reported%s%s%s", what, (e & 1) ? " [payload buffer too small]" : "",
@@ -627,36 +629,48 @@ static bool encode_batch_on_ctx(Ctx* c, const uint8_t* const* frames, int n_fram
     if (!ok) fail("encode_batch: out of page-locked host memory");
     int per_group = (int) (SUB_BYTES / fs);
     if (per_group < 1) per_group = 1;
-    auto body = [&]() -> bool {
-        CU(cudaMemsetAsync(c->d_run, 0, 8, c->stream));
-        int gi = 0;
-        for (int f0 = 0; f0 < n_mine; f0 += per_group, gi++) {
-            const int f1 = f0 + per_group < n_mine ? f0 + per_group : n_mine;
-            for (int f = f0; f < f1; f++)
-                CU(cudaMemcpyAsync(c->in.p + (size_t) f * fs, frames[first + (size_t) f * step], frame_bytes, cudaMemcpyHostToDevice,
-                                   c->copy_stream));
-            cudaEvent_t ev = c->ev[gi % MAX_SUB];
-            CU(cudaEventRecord(ev, c->copy_stream));
-            CU(cudaStreamWaitEvent(c->stream, ev, 0));
-            if (!encode_dev_impl(c, c->in.p + (size_t) f0 * fs, width, height, row_stride, 0, height, 0, mbh, c->out.p, cap, nullptr,
-                                 nullptr, nullptr, c->stream, c->d_run, f1 - f0, (long long) fs, d_off + f0))
-                return false;
-        }
-        CU(cudaMemcpyAsync(h_off, d_off, (size_t) (n_mine + 1) * 8, cudaMemcpyDeviceToHost, c->stream));
-        if (!check_err(c, c->stream, "encode_batch")) return false;
-        for (int f = 0; f < n_mine; f++) {
+    // Groups are queued one ahead: while group g uploads, the host waits for group g-1's kernels (they finish right
+    // behind its upload), reads that group's frame offsets, takes a result block per frame and queues the payload
+    // copies on the third stream (PCIe is full duplex).
+    auto ship = [&](int f0, int f1, cudaEvent_t done) -> bool {
+        CU(cudaEventSynchronize(done));
+        for (int f = f0; f < f1; f++) {
             const size_t n = (size_t) (h_off[f + 1] - h_off[f]);
             const int i = first + f * step;
             payloads[i] = static_cast<uint8_t*>(pool_get(n));
             if (!payloads[i]) return fail("encode_batch: out of page-locked host memory");
             payload_lens[i] = n;
-            CU(cudaMemcpyAsync(payloads[i], c->out.p + h_off[f], n, cudaMemcpyDeviceToHost, c->stream));
+            CU(cudaMemcpyAsync(payloads[i], c->out.p + h_off[f], n, cudaMemcpyDeviceToHost, c->back_stream));
         }
-        CU(cudaStreamSynchronize(c->stream));
+        return true;
+    };
+    auto body = [&]() -> bool {
+        CU(cudaMemsetAsync(c->d_run, 0, 8, c->stream));
+        int gi = 0, prev_f0 = -1, prev_f1 = -1;
+        cudaEvent_t prev_done = nullptr;
+        for (int f0 = 0; f0 < n_mine; f0 += per_group, gi++) {
+            const int f1 = f0 + per_group < n_mine ? f0 + per_group : n_mine;
+            for (int f = f0; f < f1; f++)
+                CU(cudaMemcpyAsync(c->in.p + (size_t) f * fs, frames[first + (size_t) f * step], frame_bytes, cudaMemcpyHostToDevice,
+                                   c->copy_stream));
+            cudaEvent_t ev = c->ev[gi % MAX_SUB], done = c->ev_done[gi % MAX_SUB];
+            CU(cudaEventRecord(ev, c->copy_stream));
+            CU(cudaStreamWaitEvent(c->stream, ev, 0));
+            if (!encode_dev_impl(c, c->in.p + (size_t) f0 * fs, width, height, row_stride, 0, height, 0, mbh, c->out.p, cap, nullptr,
+                                 nullptr, nullptr, c->stream, c->d_run, f1 - f0, (long long) fs, d_off + f0))
+                return false;
+            CU(cudaMemcpyAsync(h_off + f0, d_off + f0, (size_t) (f1 - f0 + 1) * 8, cudaMemcpyDeviceToHost, c->stream));
+            CU(cudaEventRecord(done, c->stream));
+            if (prev_done && !ship(prev_f0, prev_f1, prev_done)) return false;
+            prev_f0 = f0; prev_f1 = f1; prev_done = done;
+        }
+        if (prev_done && !ship(prev_f0, prev_f1, prev_done)) return false;
+        if (!check_err(c, c->stream, "encode_batch")) return false;
+        CU(cudaStreamSynchronize(c->back_stream));
         return true;
     };
     ok = ok && body();
-    if (!ok) cudaStreamSynchronize(c->stream);           // nothing may still be copying into blocks the caller is about to release
+    if (!ok) { cudaStreamSynchronize(c->stream); cudaStreamSynchronize(c->back_stream); }   // nothing may still be copying into blocks the caller is about to release
     if (h_off) pool_put(h_off);
     return ok;
 }
