@@ -381,6 +381,27 @@ def run_extras(codec, torch, dev, args) -> dict:
                 "decode_standalone_mpixel_per_s": round(w * h / ms_d / 1e3, 1),
                 "decode_with_encoder_offsets_mpixel_per_s": round(w * h / ms_s / 1e3, 1),
                 "decode_algorithmic_GBps": round((3 * w * h + n) / ms_d / 1e6, 1)}
+            if kind == "photo":
+                # the same decode end to end through gpu_codec_decode_to_bgr: payload up, pixels down (pinned buffers)
+                import ctypes as C
+                import numpy as np
+                lib = codec.load()
+                hp, hd = lib.gpu_codec_host_alloc(n), lib.gpu_codec_host_alloc(h * stride)
+                if hp and hd:
+                    hpay = np.ctypeslib.as_array(C.cast(hp, C.POINTER(C.c_uint8)), shape=(n,))
+                    hdst = np.ctypeslib.as_array(C.cast(hd, C.POINTER(C.c_uint8)), shape=(h * stride,))
+                    torch.from_numpy(hpay).copy_(payload[:n])
+                    torch.cuda.synchronize()
+                    codec.decode_to_bgr(hpay, w, h, stride, out=hdst)
+                    t0 = time.perf_counter()
+                    for _ in range(5):
+                        codec.decode_to_bgr(hpay, w, h, stride, out=hdst)
+                    ex[f"8192x8192_{kind}"]["decode_e2e_mpixel_per_s"] = round(w * h * 5 / (time.perf_counter() - t0) / 1e6, 1)
+                    ok = bool((torch.from_numpy(hdst).to(dev) == dst).all().item())
+                    ex[f"8192x8192_{kind}"]["decode_e2e_matches_device_path"] = ok
+                for ptr in (hp, hd):
+                    if ptr:
+                        lib.gpu_codec_host_free(C.c_void_p(ptr))
             del rows, payload, dst
     except Exception as e:                      # extras never fail the headline
         ex["error"] = repr(e)
