@@ -157,3 +157,30 @@ def test_port_vs_reference_direct(port, ref):
             c = ref.transform(b, ch)
             assert (c == port.transform(b, ch)).all()
             assert (ref.inverse_transform(c, ch) == port.inverse_transform(c, ch)).all()
+
+
+def test_chunk_starts_follow_eight_zero_bits(port):
+    """The decoder's boundary discovery only parses from positions whose two preceding bytes hold 8 consecutive
+    zero bits ending inside the last byte (the end-of-block symbol, rle.c:106, then at most 7 padding bits,
+    rle.c:107).  Every real chunk start must satisfy that, whatever the content."""
+    for kind, w, h, seed in (("photo", 320, 176, 3), ("noise", 160, 96, 4), ("flat", 64, 48, 5), ("photo", 37, 21, 6)):
+        rows = synth.frame_bgr_bottomup(kind, w, h, synth.SEED_BASE + seed)
+        p, _, lens = port.encode_bgr(rows, w, h, synth.bmp_stride(w), want_coefs=True)
+        b = np.asarray(p, dtype=np.uint32)
+        starts = np.cumsum(lens)[:-1].astype(np.int64)                  # every chunk start but the first
+        assert (starts >= 3).all()
+        win = (b[starts - 2] << 8) | b[starts - 1]
+        z = ~win & 0xFFFF
+        r = z & (z >> 1)
+        r &= r >> 2
+        r &= r >> 4
+        assert ((r & 0xFF) != 0).all(), kind
+        # and the predicate does prune: most positions fail it
+        allpos = np.arange(3, b.size)
+        win = (b[allpos - 2] << 8) | b[allpos - 1]
+        z = ~win & 0xFFFF
+        r = z & (z >> 1)
+        r &= r >> 2
+        r &= r >> 4
+        if kind != "flat":
+            assert ((r & 0xFF) != 0).mean() < 0.6
