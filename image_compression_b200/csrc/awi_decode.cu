@@ -5,9 +5,11 @@
 // EOB is not byte aligned inside a chunk) and each DC is a running sum (rle.c:123-128).
 // Here both become scans:
 //
-//   1  dec_scan_segments   every byte offset p of a 2 KB segment speculatively parses the
-//                          chunk that would start there -> L[p]; then each of the 184
-//                          possible entry offsets walks the segment: entry -> (exit, #chunks)
+//   1  dec_scan_segments   per 2 KB segment: the byte offsets that can follow an end-of-block (8 zero
+//                          bits ending in the previous byte) are collected, each speculatively
+//                          parses the chunk that would start there -> L[p]; pointer jumping over
+//                          that list gives, for each of the 184 possible entry offsets,
+//                          entry -> (exit, #chunks)
 //   2  dec_compose         32-ary tree of those maps (function composition is associative)
 //   3  dec_expand          top-down: true entry offset + first chunk index of every node
 //   4  dec_emit_offsets    per segment (one lane each): walk from the true entry, write chunk_off[]
