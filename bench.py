@@ -18,6 +18,10 @@ of the device-side time.
 `cpu_baseline` the reference's own C code (oracle/_ref, single thread — the reference has no
             threads) on a bounded band of the same frame, timed on this box's host.
 `--impl reference` times that reference code on all host cores (one band per thread).
+`extras`    secondary numbers, never the headline: at N = 1 noise-content encode and the 8192x8192 decode
+            (device-resident and end to end); at N > 1 ONE 16384x16384 frame cut into N macroblock-row stripes,
+            a stripe per GPU (configs[2] read literally, strong scaling) with the check that the stripes' byte
+            lengths add up to the whole frame's payload.
 """
 from __future__ import annotations
 
@@ -321,6 +325,34 @@ def run_ours(args, width, height, frames_per_rank, workload_desc) -> dict | None
     extras = {}
     if rank == 0 and world == 1 and not args.no_extras:
         extras = run_extras(codec, torch, dev, args)
+    if world > 1 and frames_per_rank == 1 and not args.no_extras:
+        # configs[2] read literally: ONE frame (rank 0's), cut into macroblock-row stripes, a stripe per GPU
+        # (strong scaling; every rank holds the frame and encodes rows [r0, r1) with their halo row).  The
+        # stripes' byte lengths must add up to the whole frame's payload length.
+        codec.synth_dev(0, rows[0], width, height, stride, kind, seed, 0)
+        mbh = (height + 15) // 16
+        r0, r1 = mbh * rank // world, mbh * (rank + 1) // world
+        slen = torch.zeros(1, dtype=torch.int64, device=dev)
+        for _ in range(3):
+            codec.encode_dev(0, rows[0], width, height, stride, payload, slen, mb_rows=(r0, r1))
+        barrier()
+        ev0.record()
+        for _ in range(args.steps):
+            codec.encode_dev(0, rows[0], width, height, stride, payload, slen, mb_rows=(r0, r1))
+        ev1.record()
+        barrier()
+        codec.sync_check(0)
+        ts = torch.tensor([ev0.elapsed_time(ev1) / args.steps], dtype=torch.float64, device=dev)
+        tot = slen.clone()
+        dist.all_reduce(ts, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+        whole = torch.tensor([payload_bytes if rank == 0 else 0], dtype=torch.int64, device=dev)
+        dist.all_reduce(whole, op=dist.ReduceOp.SUM)
+        extras = {"one_frame_in_stripes": {
+            "ms_per_frame": round(float(ts.item()), 4),
+            "mpixel_per_s": round(width * height / (float(ts.item()) * 1e-3) / 1e6, 1),
+            "scaling": "strong", "stripes": world,
+            "stripe_bytes_sum_equals_frame_payload": bool(int(tot.item()) == int(whole.item()))}}
 
     out = None
     if rank == 0:
