@@ -720,7 +720,9 @@ __global__ void __launch_bounds__(1024) enc_scan_tiles(const uint2* __restrict__
                                                        unsigned long long* __restrict__ tile_off,
                                                        unsigned long long* __restrict__ out_len,
                                                        unsigned long long* __restrict__ chain,
-                                                       unsigned long long out_cap, unsigned int* err) {
+                                                       unsigned long long out_cap, unsigned int* err,
+                                                       unsigned long long* __restrict__ out_len_user,
+                                                       unsigned int* __restrict__ stage_cursor) {
     __shared__ unsigned long long wsum[32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int per = ((n_tiles + 31) / 32 + 31) & ~31;               // tiles per warp, a multiple of 32
@@ -743,6 +745,8 @@ __global__ void __launch_bounds__(1024) enc_scan_tiles(const uint2* __restrict__
         wsum[lane] = base + wi - w;
         if (lane == 31) {
             *out_len = base + wi;
+            if (out_len_user != nullptr) *out_len_user = base + wi;
+            *stage_cursor = 0u;            // every tile of this launch has reserved its room: ready for the next launch
             if (chain != nullptr) *chain = base + wi;
             if (base + wi > out_cap) atomicOr(err, 1u);
         }
@@ -820,7 +824,8 @@ cudaError_t launch_encode(const EncParams& P, int n_tiles, cudaStream_t stream) 
     if (Q.tiles_per_frame <= 0) { Q.tiles_per_frame = n_tiles; Q.frame_stride = 0; }      // a single frame
     awi_encode_kernel<<<n_tiles, THREADS, sizeof(EncSmem), stream>>>(Q);
     if (P.stage != nullptr) {
-        enc_scan_tiles<<<1, 1024, 0, stream>>>(P.tile_info, n_tiles, P.tile_off, P.out_len, P.chain, P.out_cap, P.err);
+        enc_scan_tiles<<<1, 1024, 0, stream>>>(P.tile_info, n_tiles, P.tile_off, P.out_len, P.chain, P.out_cap, P.err,
+                                               P.out_len_user, P.stage_cursor);
         enc_gather_tiles<<<(n_tiles + 7) / 8, 256, 0, stream>>>(P.stage, P.tile_info, P.tile_off, n_tiles, P.out, P.out_len,
                                                                  P.out_cap, P.chunk_off, Q.tiles_per_frame,
                                                                  (P.mb1 - P.mb0) * 6, P.frame_off);

@@ -48,6 +48,7 @@ struct EncParams {
     uint8_t* out;                 // payload bytes for this range
     unsigned long long out_cap;
     unsigned long long* out_len;  // payload length, written by the last tile
+    unsigned long long* out_len_user;   // two-pass mode, optional: a second place to write it
     // single-pass mode (stage == nullptr): decoupled look-back
     unsigned long long* desc;     // one look-back descriptor per tile, zeroed before launch
     unsigned int* ticket;         // zeroed before launch
@@ -55,7 +56,7 @@ struct EncParams {
     // enc_scan_tiles + enc_gather_tiles move them to their payload offsets
     uint8_t* stage;               // 16-byte aligned
     unsigned long long stage_cap_units;   // capacity in 16-byte units
-    unsigned int* stage_cursor;   // zeroed before launch
+    unsigned int* stage_cursor;   // zero before the first launch; enc_scan_tiles leaves it at zero again
     uint2* tile_info;             // per tile: (staging offset in units, bytes)
     unsigned long long* tile_off; // per tile: payload offset
     unsigned long long* chain;    // optional in/out: payload offset to start at / ended at (sub-stripes of one frame)

@@ -239,8 +239,11 @@ bool encode_dev_impl(Ctx* c, const uint8_t* d_rows, int width, int height, long 
     // another), then a scan + gather place them; scratch = header + (where,bytes) + offset per tile
     const size_t ws_bytes = ENC_WS_HEADER + (size_t) n_tiles * 16;
     const size_t stage_bytes = cap + (size_t) n_tiles * 16 + 256;
+    const size_t ws_before = c->enc_ws.bytes;
     if (!ensure(c->enc_ws, ws_bytes) || !ensure(c->enc_stage, stage_bytes)) return false;
-    CU(cudaMemsetAsync(c->enc_ws.p, 0, ENC_WS_HEADER, st));
+    // the staging cursor must be zero when a launch starts: once here for a fresh buffer, afterwards the scan
+    // kernel of every launch leaves it at zero (one operation less per call)
+    if (c->enc_ws.bytes != ws_before) CU(cudaMemset(c->enc_ws.p, 0, ENC_WS_HEADER));
 
     awi::EncParams P{};
     // address of bottom-up row 0 of the full frame, had the whole frame been resident
@@ -272,8 +275,8 @@ bool encode_dev_impl(Ctx* c, const uint8_t* d_rows, int width, int height, long 
     P.err = c->d_err;
     P.chunk_off = d_chunk_off;
     P.qcoef = d_qcoef;
+    P.out_len_user = reinterpret_cast<unsigned long long*>(d_len);
     CU(awi::launch_encode(P, n_tiles, st));
-    if (d_len) CU(cudaMemcpyAsync(d_len, c->enc_ws.p, 8, cudaMemcpyDeviceToDevice, st));
     return true;
 }
 
