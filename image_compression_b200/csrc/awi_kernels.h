@@ -59,7 +59,8 @@ struct EncParams {
     unsigned int* stage_cursor;   // zero before the first launch; enc_scan_tiles leaves it at zero again
     uint2* tile_info;             // per tile: (staging offset in units, bytes)
     unsigned long long* tile_off; // per tile: payload offset
-    unsigned long long* chain;    // optional in/out: payload offset to start at / ended at (sub-stripes of one frame)
+    const unsigned long long* chain_in;   // optional: payload offset to start at (sub-stripes of one frame, groups of a batch)
+    unsigned long long* chain_out;        // optional: where the payload ended (a different word than chain_in)
     unsigned int* err;            // bit 0: out_cap too small
     uint32_t* chunk_off;          // optional: byte offset of every chunk in `out`
     int8_t* qcoef;                // optional: quantised coefficients, 64 per chunk, scan order

@@ -59,7 +59,8 @@ struct Ctx {
     unsigned long long* h_chain = nullptr;    // pinned: payload length after each sub-stripe
     Buf enc_ws, enc_stage, dec_ws, in, out, frame_off;
     unsigned int* d_err = nullptr;
-    unsigned long long* d_run = nullptr;      // running payload offset of a frame encoded in sub-stripes
+    unsigned long long* d_run = nullptr;      // two words: running payload offset of a frame encoded in sub-stripes, read from one
+                                              // and written to the other by each launch (alternating)
     uint64_t* h_len = nullptr;                // pinned
     std::mutex mu;
 };
@@ -217,7 +218,7 @@ __global__ void colour_kernel(const uint8_t* in, size_t n, int inverse, uint8_t*
 
 bool encode_dev_impl(Ctx* c, const uint8_t* d_rows, int width, int height, long long stride, int wy0, int wy1,
                      int r0, int r1, uint8_t* d_payload, size_t cap, uint64_t* d_len, uint32_t* d_chunk_off,
-                     int8_t* d_qcoef, cudaStream_t st, unsigned long long* d_chain = nullptr, int n_frames = 1,
+                     int8_t* d_qcoef, cudaStream_t st, unsigned long long* d_chain = nullptr, int chain_slot = 0, int n_frames = 1,
                      long long frame_stride = 0, unsigned long long* d_frame_off = nullptr) {
     if (width <= 0 || height <= 0) return fail("encode: bad geometry %dx%d", width, height);
     if (stride < 3ll * width) return fail("encode: row_stride %lld < 3*width", stride);
@@ -267,7 +268,8 @@ bool encode_dev_impl(Ctx* c, const uint8_t* d_rows, int width, int height, long 
     P.stage_cursor = reinterpret_cast<unsigned int*>(c->enc_ws.p + 16);
     P.tile_info = reinterpret_cast<uint2*>(c->enc_ws.p + ENC_WS_HEADER);
     P.tile_off = reinterpret_cast<unsigned long long*>(c->enc_ws.p + ENC_WS_HEADER + (size_t) n_tiles * 8);
-    P.chain = d_chain;
+    P.chain_in = d_chain ? d_chain + (chain_slot & 1) : nullptr;
+    P.chain_out = d_chain ? d_chain + ((chain_slot & 1) ^ 1) : nullptr;
     P.compact_cap = g_selftest_compact_cap;
     P.tiles_per_frame = tiles_per_frame;
     P.frame_stride = frame_stride;
@@ -365,7 +367,7 @@ bool gpu_codec_init_devices(const int* ids, int n) {
         g_ctx.push_back(c);
         if (cudaSetDevice(c->dev) != cudaSuccess || cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess ||
             cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking) != cudaSuccess ||
-            cudaMalloc(&c->d_run, 8) != cudaSuccess || !make_events(c) ||
+            cudaMalloc(&c->d_run, 16) != cudaSuccess || !make_events(c) ||
             cudaMalloc(&c->d_err, 4) != cudaSuccess || cudaMemset(c->d_err, 0, 4) != cudaSuccess ||
             cudaMallocHost(&c->h_len, 64) != cudaSuccess) {
             cudaError_t e = cudaGetLastError();
@@ -428,7 +430,7 @@ bool gpu_codec_encode_batch_bgr_dev(int ctx, const uint8_t* d_frames, int n_fram
     if (!d_frame_off) return fail("encode_batch: null device pointer");
     const int mbh = (height + 15) / 16;
     return encode_dev_impl(c, d_frames, width, height, row_stride, 0, height, 0, mbh, d_payload, payload_cap, nullptr, nullptr,
-                           nullptr, (cudaStream_t) stream, nullptr, n_frames, frame_stride,
+                           nullptr, (cudaStream_t) stream, nullptr, 0, n_frames, frame_stride,
                            reinterpret_cast<unsigned long long*>(d_frame_off));
 }
 
@@ -496,7 +498,7 @@ static bool encode_stripe_async(Ctx* c, const uint8_t* bmp_rows, int width, int 
     if (n_sub > MAX_SUB) n_sub = MAX_SUB;
     if (n_sub > R1 - R0) n_sub = R1 - R0;
     if (n_sub < 1) n_sub = 1;
-    CU(cudaMemsetAsync(c->d_run, 0, 8, c->stream));
+    CU(cudaMemsetAsync(c->d_run, 0, 16, c->stream));
     int y_done = y_lo;                                   // rows [y_lo, y_done) are on their way
     for (int s = 0; s < n_sub; s++) {
         const int r0 = R0 + (int) ((long long) (R1 - R0) * s / n_sub), r1 = R0 + (int) ((long long) (R1 - R0) * (s + 1) / n_sub);
@@ -511,12 +513,12 @@ static bool encode_stripe_async(Ctx* c, const uint8_t* bmp_rows, int width, int 
         CU(cudaEventRecord(c->ev[s], c->copy_stream));
         CU(cudaStreamWaitEvent(c->stream, c->ev[s], 0));
         if (!encode_dev_impl(c, c->in.p, width, height, row_stride, y_lo, y_hi, r0, r1, c->out.p, cap, nullptr, nullptr,
-                             nullptr, c->stream, c->d_run))
+                             nullptr, c->stream, c->d_run, s))
             return false;
-        CU(cudaMemcpyAsync(c->h_chain + s, c->d_run, 8, cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaMemcpyAsync(c->h_chain + s, c->d_run + ((s & 1) ^ 1), 8, cudaMemcpyDeviceToHost, c->stream));
         CU(cudaEventRecord(c->ev_done[s], c->stream));
     }
-    CU(cudaMemcpyAsync(c->h_len, c->d_run, 8, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaMemcpyAsync(c->h_len, c->d_run + (n_sub & 1), 8, cudaMemcpyDeviceToHost, c->stream));
     if (n_sub_out) *n_sub_out = n_sub;
     return true;
 }
@@ -648,7 +650,7 @@ static bool encode_batch_on_ctx(Ctx* c, const uint8_t* const* frames, int n_fram
         return true;
     };
     auto body = [&]() -> bool {
-        CU(cudaMemsetAsync(c->d_run, 0, 8, c->stream));
+        CU(cudaMemsetAsync(c->d_run, 0, 16, c->stream));
         int gi = 0, prev_f0 = -1, prev_f1 = -1;
         cudaEvent_t prev_done = nullptr;
         for (int f0 = 0; f0 < n_mine; f0 += per_group, gi++) {
@@ -660,7 +662,7 @@ static bool encode_batch_on_ctx(Ctx* c, const uint8_t* const* frames, int n_fram
             CU(cudaEventRecord(ev, c->copy_stream));
             CU(cudaStreamWaitEvent(c->stream, ev, 0));
             if (!encode_dev_impl(c, c->in.p + (size_t) f0 * fs, width, height, row_stride, 0, height, 0, mbh, c->out.p, cap, nullptr,
-                                 nullptr, nullptr, c->stream, c->d_run, f1 - f0, (long long) fs, d_off + f0))
+                                 nullptr, nullptr, c->stream, c->d_run, gi, f1 - f0, (long long) fs, d_off + f0))
                 return false;
             CU(cudaMemcpyAsync(h_off + f0, d_off + f0, (size_t) (f1 - f0 + 1) * 8, cudaMemcpyDeviceToHost, c->stream));
             CU(cudaEventRecord(done, c->stream));
