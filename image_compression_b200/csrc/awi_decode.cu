@@ -11,7 +11,8 @@
 //                          that list gives, for each of the 184 possible entry offsets,
 //                          entry -> (exit, #chunks)
 //   2  dec_compose         32-ary tree of those maps (function composition is associative)
-//   3  dec_expand          top-down: true entry offset + first chunk index of every node
+//   3  dec_root_expand,    top-down: true entry offset + first chunk index of every node (the root check and
+//      dec_expand          the small upper levels in one CTA, the segment level in parallel)
 //   4  dec_emit_offsets    per segment (one lane each): walk from the true entry, write chunk_off[]
 //   5  dec_dc_*            per-stream (chunk index mod 6) inclusive scan of the DC diffs
 //   6  dec_reconstruct     8 macroblocks per CTA: parse -> dequantise -> IDCT in the
@@ -241,13 +242,35 @@ __global__ void dec_expand(const unsigned long long* __restrict__ pre, long long
     child[c] = st;
 }
 
-__global__ void dec_root(const unsigned long long* __restrict__ top_table, NodeState* __restrict__ root,
-                         unsigned long long expect_chunks, unsigned int* err) {
-    if (threadIdx.x != 0 || blockIdx.x != 0) return;
-    unsigned long long t = top_table[0];
-    NodeState st; st.first_chunk = 0; st.entry = 0; st.ok = 1;
-    if (!(t & ENT_OK) || ent_cnt(t) != expect_chunks) { st.ok = 0; atomicOr(err, 2u); }
-    root[0] = st;
+// The root check and the expansion of the small upper levels (down to level 1) in one CTA: a launch per
+// level is all latency there.
+struct TopLevels {
+    int levels;
+    long long n_node[16];
+    const unsigned long long* pre[16];            // pre[lv]: states in front of the children (level lv-1) of level lv
+    NodeState* state[16];
+};
+__global__ void __launch_bounds__(256) dec_root_expand(const unsigned long long* __restrict__ top_table, TopLevels T,
+                                                       unsigned long long expect_chunks, unsigned int* err) {
+    if (threadIdx.x == 0) {
+        const unsigned long long t = top_table[0];
+        NodeState st; st.first_chunk = 0; st.entry = 0; st.ok = 1;
+        if (!(t & ENT_OK) || ent_cnt(t) != expect_chunks) { st.ok = 0; atomicOr(err, 2u); }
+        T.state[T.levels - 1][0] = st;
+    }
+    __syncthreads();
+    for (int lv = T.levels - 1; lv >= 2; lv--) {
+        for (long long c = threadIdx.x; c < T.n_node[lv - 1]; c += 256) {
+            NodeState st = T.state[lv][c / FAN];
+            if (st.ok) {
+                const unsigned long long p = T.pre[lv][c * MAXCH + st.entry];
+                if (p & ENT_OK) { st.first_chunk += ent_cnt(p); st.entry = ent_exit(p); }
+                else st.ok = 0;
+            }
+            T.state[lv - 1][c] = st;
+        }
+        __syncthreads();                                  // this CTA's global writes, read by this CTA
+    }
 }
 
 // ---------------------------------------------------------------- 4: offsets
@@ -296,16 +319,29 @@ __device__ __forceinline__ int dc_diff_at(const uint8_t* __restrict__ payload, u
     return raw > 2047 ? raw - 4095 : raw;
 }
 
-template <int MODE>   // 0: tile sums   1: apply (inclusive scan + tile base)
+template <int MODE>   // 0: tile sums   1: apply (inclusive scan + tile base)   2: apply, adding up the sums of the tiles in front itself
 __global__ void __launch_bounds__(DCT_MB) dec_dc_tile(const uint8_t* __restrict__ payload,
                                                       const uint32_t* __restrict__ chunk_off, long long n_mb,
                                                       int* __restrict__ tile_sum, const int* __restrict__ tile_base,
                                                       int* __restrict__ dcabs, unsigned long long P,
                                                       const unsigned int* __restrict__ err) {
     __shared__ int wsum[DCT_MB / 32][6];
+    __shared__ int bsum[DCT_MB / 32][6];
     if (*reinterpret_cast<const volatile unsigned int*>(err) != 0) return;     // boundaries unknown: nothing to scan
     const long long mb = (long long) blockIdx.x * DCT_MB + threadIdx.x;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (MODE == 2) {      // few tiles: every CTA sums what lies in front of it (tile_sum[] is `tile_base` here) instead of a scan launch
+        int s[6] = { 0, 0, 0, 0, 0, 0 };
+        for (long long t = threadIdx.x; t < (long long) blockIdx.x; t += DCT_MB)
+#pragma unroll
+            for (int k = 0; k < 6; k++) s[k] += tile_base[t * 6 + k];
+#pragma unroll
+        for (int k = 0; k < 6; k++) {
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) s[k] += __shfl_xor_sync(0xffffffffu, s[k], o);
+            if (lane == 0) bsum[warp][k] = s[k];
+        }
+    }
     int v[6];
 #pragma unroll
     for (int k = 0; k < 6; k++) v[k] = mb < n_mb ? dc_diff_at(payload, chunk_off[mb * 6 + k], P) : 0;
@@ -329,7 +365,9 @@ __global__ void __launch_bounds__(DCT_MB) dec_dc_tile(const uint8_t* __restrict_
         if (mb < n_mb) {
 #pragma unroll
             for (int k = 0; k < 6; k++) {
-                int base = tile_base[(long long) blockIdx.x * 6 + k];
+                int base = 0;
+                if (MODE == 2) { for (int w = 0; w < DCT_MB / 32; w++) base += bsum[w][k]; }
+                else base = tile_base[(long long) blockIdx.x * 6 + k];
                 for (int w = 0; w < warp; w++) base += wsum[w][k];
                 dcabs[mb * 6 + k] = base + v[k];
             }
@@ -672,11 +710,12 @@ cudaError_t launch_decode(const DecParams& P, void* workspace, size_t workspace_
         auto pre = [&](int lv) { return reinterpret_cast<unsigned long long*>(ws + Lo.off_pre[lv]); };
         for (int lv = 1; lv < Lo.levels; lv++)
             dec_compose<<<(unsigned) Lo.n_node[lv], 192, FAN * MAXCH * 8, stream>>>(table(lv - 1), Lo.n_node[lv - 1], table(lv), pre(lv));
-        dec_root<<<1, 32, 0, stream>>>(table(Lo.levels - 1), state(Lo.levels - 1), (unsigned long long) n_chunks, err);
-        for (int lv = Lo.levels - 1; lv >= 1; lv--) {
-            const long long nc = Lo.n_node[lv - 1];
-            dec_expand<<<(unsigned) ((nc + 127) / 128), 128, 0, stream>>>(pre(lv), nc, state(lv), state(lv - 1));
-        }
+        TopLevels T{};
+        T.levels = Lo.levels;
+        for (int lv = 0; lv < Lo.levels; lv++) { T.n_node[lv] = Lo.n_node[lv]; T.pre[lv] = pre(lv); T.state[lv] = state(lv); }
+        dec_root_expand<<<1, 256, 0, stream>>>(table(Lo.levels - 1), T, (unsigned long long) n_chunks, err);
+        if (Lo.levels >= 2)
+            dec_expand<<<(unsigned) ((Lo.n_node[0] + 127) / 128), 128, 0, stream>>>(pre(1), Lo.n_node[0], state(1), state(0));
         dec_emit_offsets<<<(unsigned) ((Lo.n_seg + EMIT_SEGS - 1) / EMIT_SEGS), 256, EMIT_SEGS * SEG, stream>>>(
             Lg, P.payload_len, state(0), Lo.n_seg, chunk_off, (unsigned long long) n_chunks);
     } else {
@@ -689,8 +728,12 @@ cudaError_t launch_decode(const DecParams& P, void* workspace, size_t workspace_
 
     if (!reuse_index) {
     dec_dc_tile<0><<<(unsigned) Lo.n_dct, DCT_MB, 0, stream>>>(P.payload, chunk_off, n_mb, tile_sum, nullptr, nullptr, P.payload_len, err);
-    dec_dc_scan_tiles<<<1, 1024, 0, stream>>>(tile_sum, Lo.n_dct, tile_base);
-    dec_dc_tile<1><<<(unsigned) Lo.n_dct, DCT_MB, 0, stream>>>(P.payload, chunk_off, n_mb, nullptr, tile_base, dcabs, P.payload_len, err);
+    if (Lo.n_dct <= 1024) {     // up to 8192x8192: the scan of the tile sums is folded into the second pass
+        dec_dc_tile<2><<<(unsigned) Lo.n_dct, DCT_MB, 0, stream>>>(P.payload, chunk_off, n_mb, nullptr, tile_sum, dcabs, P.payload_len, err);
+    } else {
+        dec_dc_scan_tiles<<<1, 1024, 0, stream>>>(tile_sum, Lo.n_dct, tile_base);
+        dec_dc_tile<1><<<(unsigned) Lo.n_dct, DCT_MB, 0, stream>>>(P.payload, chunk_off, n_mb, nullptr, tile_base, dcabs, P.payload_len, err);
+    }
     }
 
     const int tiles_per_row = (P.mbw + REC_MB - 1) / REC_MB;
