@@ -93,7 +93,8 @@ __global__ void __launch_bounds__(256) dec_scan_segments(const uint8_t* __restri
     // (bitrw.c:72-76): so the two bytes in front of a chunk start hold 8 consecutive zero bits that end inside
     // the last one.  Positions without that can never be reached by a parse (about two in three on photo-like
     // streams, four in five on noise); the others are collected, in order, and everything after this works on
-    // that list.  Thread t looks at positions 8t .. 8t+7.
+    // that list.  Thread t looks at positions 8t .. 8t+7.  (L[] is only ever read at positions a chain visits,
+    // and those are candidates: the others are not written at all.)
     unsigned flags = 0;
     {
         const int p0 = 8 * tid;
@@ -114,7 +115,6 @@ __global__ void __launch_bounds__(256) dec_scan_segments(const uint8_t* __restri
                     r &= r >> 4;                                         // bit i: window bits i..i+7 are all zero
                     cand = (r & 0xffu) != 0;                             // the run ends inside the last byte
                 }
-                if (!cand) Lg[g] = 0;
             }
             flags |= (cand ? 1u : 0u) << k;
             b2 = b1;
