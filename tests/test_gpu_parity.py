@@ -347,3 +347,53 @@ def test_extreme_aspect_ratios(gpu, port):
         got = gpu.encode_bgr(rows, w, h, stride)
         assert got == want.tobytes(), (w, h)
         assert gpu.decode_to_bgr(got, w, h, stride).tobytes() == port.decode(want, w, h, stride)[0].tobytes()
+
+
+def test_guard_bands_stay_untouched(gpu, port):
+    """compute-sanitizer is not available on this pool: every device buffer the codec writes is given guard bands
+    here (a known pattern in front of and behind it), over ragged sizes and both content extremes, and the bands
+    must come back intact — payload, length word, chunk offsets, coefficients on the encode side, pixel rows on the
+    decode side (exactly sized, both sinks)."""
+    import torch
+    G = 4096
+    def guarded(nbytes, dtype=torch.uint8):
+        es = torch.empty(0, dtype=dtype).element_size()
+        buf = torch.full(((nbytes + 2 * G) // es + 1,), 0x5A if dtype == torch.uint8 else 0x5A5A5A5A, dtype=dtype, device="cuda")
+        g = G // es
+        return buf, buf[g: g + nbytes // es]
+    def intact(buf, inner_elems):
+        es = buf.element_size()
+        g = G // es
+        pat = 0x5A if buf.dtype == torch.uint8 else 0x5A5A5A5A
+        return bool((buf[:g] == pat).all().item()) and bool((buf[g + inner_elems:] == pat).all().item())
+    for kind, w, h in (("noise", 530, 100), ("photo", 1024, 48), ("noise", 37, 21), ("photo", 16 * 33, 16 * 3), ("noise", 512, 16)):
+        stride = synth.bmp_stride(w)
+        rows = synth.frame_bgr_bottomup(kind, w, h, 0xA11CE07)
+        want = port.encode_bgr(rows, w, h, stride)
+        nch = ((w + 15) // 16) * ((h + 15) // 16) * 6
+        rows_buf, rows_t = guarded(rows.size)
+        rows_t.copy_(torch.from_numpy(rows.reshape(-1)).cuda())
+        pay_buf, pay = guarded(nch * 121 + 16)
+        off_buf, off = guarded(nch * 4, torch.int32)
+        q_buf, q = guarded(nch * 64)
+        ln = torch.zeros(1, dtype=torch.int64, device="cuda")
+        gpu.encode_dev(0, rows_t, w, h, stride, pay, ln, chunk_off=off, qcoef=q.view(torch.int8))
+        gpu.sync_check(0)
+        n = int(ln.item())
+        assert pay[:n].cpu().numpy().tobytes() == want.tobytes()
+        assert intact(pay_buf, pay.numel()) and intact(off_buf, off.numel()) and intact(q_buf, q.numel()) and intact(rows_buf, rows_t.numel())
+        # decode into exactly sized, guarded sinks; payload passed exactly sized too
+        p_buf, p_t = guarded(n)
+        p_t.copy_(pay[:n])
+        for rgb in (False, True):
+            nbytes = 3 * w * h if rgb else stride * h
+            d_buf, dst = guarded(nbytes)
+            gpu.decode_dev(0, p_t, n, w, h, dst, stride, rgb_topdown=rgb)
+            gpu.sync_check(0)
+            ref = port.decode(want, w, h, stride, rgb_topdown=rgb)[0]
+            got = dst.cpu().numpy()
+            if rgb:
+                assert got.tobytes() == ref.tobytes()
+            else:
+                assert (got.reshape(h, stride)[:, : 3 * w] == ref.reshape(h, stride)[:, : 3 * w]).all()
+            assert intact(d_buf, dst.numel()) and intact(p_buf, p_t.numel())
