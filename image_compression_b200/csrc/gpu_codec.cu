@@ -9,6 +9,8 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <condition_variable>
+#include <functional>
 #include <mutex>
 #include <string>
 #include <thread>
@@ -42,6 +44,7 @@ bool fail(const char* fmt, ...) {
 constexpr int MAX_SUB = 32;               // sub-stripes a frame is cut into to overlap PCIe copies with the kernels
 constexpr size_t SUB_BYTES = 48u << 20;   // aim for ~48 MB of pixels per sub-stripe
 constexpr size_t SUB_BYTES_MIN = 4u << 20;
+constexpr int RING_SLOTS = 3;              // page-locked staging slots per context for uploads from pageable memory
 constexpr size_t ENC_WS_HEADER = 256;     // [0,8) payload length, [8,12) tile ticket, [16,20) staging cursor
 
 struct Buf {
@@ -62,6 +65,12 @@ struct Ctx {
     unsigned long long* d_run = nullptr;      // two words: running payload offset of a frame encoded in sub-stripes, read from one
                                               // and written to the other by each launch (alternating)
     uint64_t* h_len = nullptr;                // pinned
+    // uploads from pageable memory go through these page-locked slots (see upload())
+    uint8_t* ring[RING_SLOTS] = { nullptr };
+    size_t ring_bytes = 0;
+    cudaEvent_t ring_ev[RING_SLOTS] = { nullptr };
+    bool ring_busy[RING_SLOTS] = { false };
+    int ring_next = 0;
     std::mutex mu;
 };
 
@@ -102,6 +111,10 @@ void destroy_ctx(Ctx* c) {
         if (b->p) cudaFree(b->p);
     if (c->d_err) cudaFree(c->d_err);
     if (c->h_len) cudaFreeHost(c->h_len);
+    for (int i = 0; i < RING_SLOTS; i++) {
+        if (c->ring[i]) cudaFreeHost(c->ring[i]);
+        if (c->ring_ev[i]) cudaEventDestroy(c->ring_ev[i]);
+    }
     delete c;
 }
 
@@ -161,6 +174,104 @@ inline int align_of(const void* p, long long stride) {
     if (a % 16 == 0 && stride % 16 == 0) return 16;
     if (a % 4 == 0 && stride % 4 == 0) return 4;
     return 1;
+}
+
+// -------------------------------------------------------------- uploads from pageable memory
+//
+// The reference reads its BMP into ordinary malloc'd memory (bmp.c:38, :125), and a drop-in caller will hand us
+// exactly that.  cudaMemcpyAsync from pageable memory is staged by the driver on one thread (5-10 GB/s measured
+// here, against 55 GB/s from page-locked memory), so such sources are staged here instead: a few page-locked
+// slots per context, filled by a small pool of copy threads while the previous slot is on the wire.
+class CopyPool {
+public:
+    static CopyPool& get() { static CopyPool* p = new CopyPool; return *p; }      // never destroyed: its threads sleep until exit
+    // dst/src are split into one piece per worker; returns when every piece is copied
+    void copy(uint8_t* dst, const uint8_t* src, size_t n) {
+        const size_t nw = workers_.size();
+        if (nw == 0 || n < (4u << 20)) { memcpy(dst, src, n); return; }
+        std::unique_lock<std::mutex> call(call_mu_);          // one parallel copy at a time
+        {
+            std::lock_guard<std::mutex> lk(mu_);
+            const size_t piece = ((n + nw - 1) / nw + 4095) & ~(size_t) 4095;
+            for (size_t i = 0; i < nw; i++) {
+                const size_t a = i * piece < n ? i * piece : n, b = a + piece < n ? a + piece : n;
+                jobs_[i] = { dst + a, src + a, b - a };
+            }
+            pending_ = (int) nw;
+            generation_++;
+        }
+        cv_.notify_all();
+        std::unique_lock<std::mutex> lk(mu_);
+        done_.wait(lk, [&] { return pending_ == 0; });
+    }
+private:
+    struct Job { uint8_t* d; const uint8_t* s; size_t n; };
+    CopyPool() {
+        unsigned hw = std::thread::hardware_concurrency();
+        unsigned nw = hw >= 16 ? 8 : (hw >= 4 ? hw / 2 : 0);
+        jobs_.resize(nw);
+        for (unsigned i = 0; i < nw; i++) workers_.emplace_back([this, i] { run(i); });
+        for (auto& t : workers_) t.detach();                  // they sleep on cv_ for the life of the process
+    }
+    void run(unsigned i) {
+        unsigned long long seen = 0;
+        while (true) {
+            Job j;
+            {
+                std::unique_lock<std::mutex> lk(mu_);
+                cv_.wait(lk, [&] { return generation_ != seen; });
+                seen = generation_;
+                j = jobs_[i];
+            }
+            if (j.n) memcpy(j.d, j.s, j.n);
+            {
+                std::lock_guard<std::mutex> lk(mu_);
+                if (--pending_ == 0) done_.notify_all();
+            }
+        }
+    }
+    std::vector<std::thread> workers_;
+    std::vector<Job> jobs_;
+    std::mutex mu_, call_mu_;
+    std::condition_variable cv_, done_;
+    unsigned long long generation_ = 0;
+    int pending_ = 0;
+};
+
+bool is_pageable(const void* p) {
+    static const bool off = getenv("GPU_CODEC_NO_STAGING") != nullptr;      // measurement knob: leave pageable memory to the driver
+    if (off) return false;
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return true; }
+    return a.type == cudaMemoryTypeUnregistered;
+}
+
+// Host -> device on the context's copy stream.  Page-locked sources go straight to the copy engine; pageable ones
+// pass through the ring (at most `ring_bytes` per slot: larger requests are cut).
+bool upload(Ctx* c, uint8_t* d_dst, const uint8_t* h_src, size_t n, bool pageable) {
+    if (!pageable) {
+        CU(cudaMemcpyAsync(d_dst, h_src, n, cudaMemcpyHostToDevice, c->copy_stream));
+        return true;
+    }
+    const size_t want = 32u << 20;
+    if (c->ring_bytes == 0) {
+        for (int i = 0; i < RING_SLOTS; i++) {
+            CU(cudaMallocHost(&c->ring[i], want));
+            CU(cudaEventCreateWithFlags(&c->ring_ev[i], cudaEventDisableTiming));
+        }
+        c->ring_bytes = want;
+    }
+    for (size_t at = 0; at < n; at += c->ring_bytes) {
+        const size_t m = n - at < c->ring_bytes ? n - at : c->ring_bytes;
+        const int slot = c->ring_next;
+        c->ring_next = (slot + 1) % RING_SLOTS;
+        if (c->ring_busy[slot]) CU(cudaEventSynchronize(c->ring_ev[slot]));      // its previous contents are on the device
+        CopyPool::get().copy(c->ring[slot], h_src + at, m);
+        CU(cudaMemcpyAsync(d_dst + at, c->ring[slot], m, cudaMemcpyHostToDevice, c->copy_stream));
+        CU(cudaEventRecord(c->ring_ev[slot], c->copy_stream));
+        c->ring_busy[slot] = true;
+    }
+    return true;
 }
 
 // -------------------------------------------------------------- small kernels
@@ -499,6 +610,7 @@ static bool encode_stripe_async(Ctx* c, const uint8_t* bmp_rows, int width, int 
     if (n_sub > R1 - R0) n_sub = R1 - R0;
     if (n_sub < 1) n_sub = 1;
     CU(cudaMemsetAsync(c->d_run, 0, 16, c->stream));
+    const bool pageable = is_pageable(bmp_rows);
     int y_done = y_lo;                                   // rows [y_lo, y_done) are on their way
     for (int s = 0; s < n_sub; s++) {
         const int r0 = R0 + (int) ((long long) (R1 - R0) * s / n_sub), r1 = R0 + (int) ((long long) (R1 - R0) * (s + 1) / n_sub);
@@ -507,7 +619,7 @@ static bool encode_stripe_async(Ctx* c, const uint8_t* bmp_rows, int width, int 
             // rows y_done..y_to-1 are the bottom-up byte range [(height-y_to)*stride, (height-y_done)*stride)
             const uint8_t* hsrc = bmp_rows + (size_t) (height - y_to) * row_stride;
             uint8_t* ddst = c->in.p + (size_t) (y_hi - y_to) * row_stride;
-            CU(cudaMemcpyAsync(ddst, hsrc, (size_t) (y_to - y_done) * row_stride, cudaMemcpyHostToDevice, c->copy_stream));
+            if (!upload(c, ddst, hsrc, (size_t) (y_to - y_done) * row_stride, pageable)) return false;
             y_done = y_to;
         }
         CU(cudaEventRecord(c->ev[s], c->copy_stream));
@@ -655,9 +767,10 @@ static bool encode_batch_on_ctx(Ctx* c, const uint8_t* const* frames, int n_fram
         cudaEvent_t prev_done = nullptr;
         for (int f0 = 0; f0 < n_mine; f0 += per_group, gi++) {
             const int f1 = f0 + per_group < n_mine ? f0 + per_group : n_mine;
-            for (int f = f0; f < f1; f++)
-                CU(cudaMemcpyAsync(c->in.p + (size_t) f * fs, frames[first + (size_t) f * step], frame_bytes, cudaMemcpyHostToDevice,
-                                   c->copy_stream));
+            for (int f = f0; f < f1; f++) {
+                const uint8_t* src = frames[first + (size_t) f * step];
+                if (!upload(c, c->in.p + (size_t) f * fs, src, frame_bytes, is_pageable(src))) return false;
+            }
             cudaEvent_t ev = c->ev[gi % MAX_SUB], done = c->ev_done[gi % MAX_SUB];
             CU(cudaEventRecord(ev, c->copy_stream));
             CU(cudaStreamWaitEvent(c->stream, ev, 0));
