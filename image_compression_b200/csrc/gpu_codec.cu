@@ -274,6 +274,49 @@ bool upload(Ctx* c, uint8_t* d_dst, const uint8_t* h_src, size_t n, bool pageabl
     return true;
 }
 
+// Device -> pageable host memory through the same ring: the copy engine fills a slot while the copy threads
+// empty the one before it.  `pend` remembers slots whose bytes still have to be moved to their destination.
+struct PendingOut { int slot; uint8_t* h_dst; size_t n; };
+bool drain_one(Ctx* c, std::vector<PendingOut>& pend) {
+    if (pend.empty()) return true;
+    const PendingOut p = pend.front();
+    pend.erase(pend.begin());
+    CU(cudaEventSynchronize(c->ring_ev[p.slot]));
+    CopyPool::get().copy(p.h_dst, c->ring[p.slot], p.n);
+    c->ring_busy[p.slot] = false;
+    return true;
+}
+bool download(Ctx* c, uint8_t* h_dst, const uint8_t* d_src, size_t n, std::vector<PendingOut>& pend) {
+    const size_t want = 32u << 20;
+    if (c->ring_bytes == 0) {
+        for (int i = 0; i < RING_SLOTS; i++) {
+            CU(cudaMallocHost(&c->ring[i], want));
+            CU(cudaEventCreateWithFlags(&c->ring_ev[i], cudaEventDisableTiming));
+        }
+        c->ring_bytes = want;
+    }
+    const size_t piece = 8u << 20;                             // small pieces: only the last one's copy-out is not overlapped
+    for (size_t at = 0; at < n; at += piece) {
+        const size_t m = n - at < piece ? n - at : piece;
+        const int slot = c->ring_next;
+        c->ring_next = (slot + 1) % RING_SLOTS;
+        while (!pend.empty() && c->ring_busy[slot]) {          // the slot still holds undelivered bytes (oldest first)
+            bool mine = false;
+            for (const PendingOut& p : pend) mine = mine || p.slot == slot;
+            if (!mine) break;
+            if (!drain_one(c, pend)) return false;
+        }
+        if (c->ring_busy[slot]) CU(cudaEventSynchronize(c->ring_ev[slot]));      // (an earlier upload from it)
+        CU(cudaMemcpyAsync(c->ring[slot], d_src + at, m, cudaMemcpyDeviceToHost, c->copy_stream));
+        CU(cudaEventRecord(c->ring_ev[slot], c->copy_stream));
+        c->ring_busy[slot] = true;
+        pend.push_back({ slot, h_dst + at, m });
+        while (pend.size() > 1)                                // deliver the piece before while this one is on the wire
+            if (!drain_one(c, pend)) return false;
+    }
+    return true;
+}
+
 // -------------------------------------------------------------- small kernels
 
 __global__ void synth_kernel(uint8_t* rows, int width, int height, long long stride, int kind, uint32_t seed, int frame) {
@@ -829,6 +872,8 @@ static bool decode_host(const uint8_t* payload, size_t len, int width, int heigh
     const long long pitch = rgb ? 3ll * width : stride;
     std::vector<std::unique_lock<std::mutex>> locks;
     for (int g = 0; g < G; g++) locks.emplace_back(g_ctx[g]->mu);
+    const bool dst_pageable = is_pageable(dst) && pitch == 3ll * width, src_pageable = is_pageable(payload) && len >= (4u << 20);
+    std::vector<std::vector<PendingOut>> pend(G);
     auto enqueue = [&](int g) -> bool {
         Ctx* c = g_ctx[g];
         int R0, R1;
@@ -837,7 +882,13 @@ static bool decode_host(const uint8_t* payload, size_t len, int width, int heigh
         const size_t out_bytes = (size_t) (y_hi - y_lo) * pitch;
         CU(cudaSetDevice(c->dev));
         if (!ensure(c->in, len + 16) || !ensure(c->out, out_bytes)) return false;
-        CU(cudaMemcpyAsync(c->in.p, payload, len, cudaMemcpyHostToDevice, c->stream));
+        if (src_pageable) {
+            if (!upload(c, c->in.p, payload, len, true)) return false;
+            CU(cudaEventRecord(c->ev_done[0], c->copy_stream));
+            CU(cudaStreamWaitEvent(c->stream, c->ev_done[0], 0));
+        } else {
+            CU(cudaMemcpyAsync(c->in.p, payload, len, cudaMemcpyHostToDevice, c->stream));
+        }
         // the stripe's rows are contiguous in both sinks; hand the kernel the address the
         // full frame's first byte would have
         uint8_t* vbase = rgb ? c->out.p - (long long) y_lo * pitch : c->out.p - (long long) (height - y_hi) * pitch;
@@ -854,7 +905,9 @@ static bool decode_host(const uint8_t* payload, size_t len, int width, int heigh
             const int ya = 16 * r0, yb = 16 * r1 < height ? 16 * r1 : height;
             const size_t rel = rgb ? (size_t) (ya - y_lo) * pitch : (size_t) (y_hi - yb) * pitch;      // offset inside the stripe buffer
             uint8_t* hdst = rgb ? dst + (size_t) ya * pitch : dst + (size_t) (height - yb) * pitch;
-            if (pitch == 3ll * width) {
+            if (dst_pageable) {
+                if (!download(c, hdst, c->out.p + rel, (size_t) (yb - ya) * pitch, pend[g])) return false;
+            } else if (pitch == 3ll * width) {
                 CU(cudaMemcpyAsync(hdst, c->out.p + rel, (size_t) (yb - ya) * pitch, cudaMemcpyDeviceToHost, c->copy_stream));
             } else {   // leave the caller's row padding bytes alone
                 CU(cudaMemcpy2DAsync(hdst, (size_t) pitch, c->out.p + rel, (size_t) pitch, (size_t) 3 * width, (size_t) (yb - ya),
@@ -867,6 +920,9 @@ static bool decode_host(const uint8_t* payload, size_t len, int width, int heigh
     for (int g = 0; g < G && ok; g++) ok = enqueue(g);
     // success or not, nothing may still be writing into the caller's buffer when this returns
     for (int g = 0; g < G; g++) {
+        cudaSetDevice(g_ctx[g]->dev);
+        while (!pend[g].empty())
+            if (!drain_one(g_ctx[g], pend[g])) { ok = false; pend[g].clear(); }
         if (!check_err(g_ctx[g], g_ctx[g]->stream, "decode")) ok = false;
         cudaSetDevice(g_ctx[g]->dev);
         if (cudaStreamSynchronize(g_ctx[g]->copy_stream) != cudaSuccess) ok = fail("decode: D2H failed");

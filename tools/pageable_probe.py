@@ -29,3 +29,20 @@ for name, buf in (("pinned", pinned), ("pageable", pageable)):
             res[name] = got
         print(f"{name}: {dt*1e3:.2f} ms, {w*h/dt/1e9:.2f} Gpixel/s, payload {ln}")
 print("identical payloads:", res["pinned"] == res["pageable"])
+
+# decode: gpu_codec_decode_to_bgr into page-locked vs ordinary memory (payload from the same kind of memory)
+pay = np.frombuffer(res["pinned"], np.uint8)
+hq = lib.gpu_codec_host_alloc(pay.size)
+pay_pinned = np.ctypeslib.as_array(C.cast(hq, C.POINTER(C.c_uint8)), shape=(pay.size,))
+pay_pinned[:] = pay
+pay_pageable = pay.copy()
+out_pageable = np.zeros(n, np.uint8)
+outs = {}
+for name, p, o in (("pinned", pay_pinned, pinned), ("pageable", pay_pageable, out_pageable)):
+    for i in range(4):
+        t = time.perf_counter()
+        codec.decode_to_bgr(p, w, h, stride, out=o)
+        dt = time.perf_counter() - t
+        print(f"decode {name}: {dt*1e3:.2f} ms, {w*h/dt/1e9:.2f} Gpixel/s")
+    outs[name] = o.copy()
+print("identical pixels:", bool((outs["pinned"] == outs["pageable"]).all()))
