@@ -131,3 +131,40 @@ def test_reference_bmp_code_linked_against_our_awi(port, tmp_path):
     assert r.returncode == 0, r.stderr
     back = (tmp_path / "back.bmp").read_bytes()
     assert back[54:] == port.decode(want, w, h)[0].tobytes()
+
+
+def test_repeated_calls_are_deterministic(port):
+    """Back-to-back calls reuse everything a context owns (staging cursor, chained offsets, page-locked slots,
+    result blocks): the same frames must give the same bytes every time, through every host entry point,
+    from page-locked and from ordinary memory, with other sizes in between."""
+    import ctypes as C
+    import torch
+    from image_compression_b200 import codec
+    codec.init([0])
+    lib = codec.load()
+    w, h = 1920, 1080
+    stride = synth.bmp_stride(w)
+    frames = [synth.frame_bgr_bottomup(k, w, h, 0xA11CE08, f).reshape(-1) for f, k in enumerate(("photo", "noise", "photo"))]
+    want = [port.encode_bgr(f, w, h, stride).tobytes() for f in frames]
+    small = synth.frame_bgr_bottomup("noise", 200, 120, 0xA11CE09).reshape(-1)
+    want_small = port.encode_bgr(small, 200, 120, synth.bmp_stride(200)).tobytes()
+    hp = lib.gpu_codec_host_alloc(frames[0].size)
+    pinned = np.ctypeslib.as_array(C.cast(hp, C.POINTER(C.c_uint8)), shape=(frames[0].size,))
+    try:
+        for it in range(12):
+            f = it % 3
+            if it % 2:
+                pinned[:] = frames[f]
+                assert codec.encode_bgr(pinned, w, h, stride) == want[f], it
+            else:
+                assert codec.encode_bgr(frames[f], w, h, stride) == want[f], it
+            if it % 4 == 1:
+                assert codec.encode_bgr(small, 200, 120, synth.bmp_stride(200)) == want_small
+            if it % 4 == 2:
+                got = codec.encode_batch_bgr(frames, w, h, stride)
+                assert [bytes(g) for g in got] == want
+            if it % 4 == 3:
+                px = codec.decode_to_bgr(np.frombuffer(want[f], np.uint8), w, h, stride)
+                assert px.tobytes() == port.decode(np.frombuffer(want[f], np.uint8), w, h, stride)[0].tobytes()
+    finally:
+        lib.gpu_codec_host_free(C.c_void_p(hp))
