@@ -397,3 +397,43 @@ def test_guard_bands_stay_untouched(gpu, port):
             else:
                 assert (got.reshape(h, stride)[:, : 3 * w] == ref.reshape(h, stride)[:, : 3 * w]).all()
             assert intact(d_buf, dst.numel()) and intact(p_buf, p_t.numel())
+
+
+def test_corrupted_streams_agree_with_oracle(gpu, port):
+    """Edited, truncated and extended payloads: the decoder accepts exactly what the oracle parses to the last byte
+    (same pixels then) and rejects the rest; the context keeps working (tools/fuzz_corrupt.py is the long version)."""
+    from image_compression_b200 import codec
+    rng = np.random.default_rng(17)
+    accepted = rejected = 0
+    for case in range(60):
+        w, h = int(rng.integers(16, 400)), int(rng.integers(16, 240))
+        stride = synth.bmp_stride(w)
+        rows = synth.frame_bgr_bottomup(("photo", "noise")[case % 2], w, h, 0xBAD0 + case)
+        p = np.array(port.encode_bgr(rows, w, h, stride), np.uint8)
+        op = case % 4
+        if op == 0:
+            for _ in range(3):
+                p[int(rng.integers(0, p.size))] = int(rng.integers(0, 256))
+        elif op == 1:
+            p[int(rng.integers(0, p.size))] ^= 1 << int(rng.integers(0, 8))
+        elif op == 2:
+            p = p[: int(rng.integers(0, p.size))].copy()
+        else:
+            p = np.concatenate([p, rng.integers(0, 256, 5).astype(np.uint8)])
+        try:
+            ref, used = port.decode(p, w, h, stride)
+            oracle_ok = used == p.size
+        except ValueError:
+            oracle_ok = False
+        try:
+            got = gpu.decode_to_bgr(p, w, h, stride)
+            gpu_ok = True
+        except codec.GpuCodecError:
+            gpu_ok = False
+        assert gpu_ok == oracle_ok, (case, w, h, op)
+        if gpu_ok:
+            assert (got.reshape(h, stride)[:, : 3 * w] == ref.reshape(h, stride)[:, : 3 * w]).all(), (case, w, h, op)
+            accepted += 1
+        else:
+            rejected += 1
+    assert accepted > 0 and rejected > 0
