@@ -63,7 +63,8 @@ const char* gpu_codec_last_error(void);
  * (12 + 63*(8+7) + 8 bits, rle.c:52-110 with |coefficient| <= 95). */
 size_t gpu_codec_max_payload_bytes(int width, int height);
 
-/* Page-locked host memory for fast transfers; optional (any host pointer works). */
+/* Page-locked host memory for the fastest transfers; optional: any host pointer works, ordinary (pageable) memory
+ * is staged through page-locked slots inside the library. */
 void* gpu_codec_host_alloc(size_t bytes);
 void gpu_codec_host_free(void* p);
 
@@ -75,19 +76,21 @@ void gpu_codec_free(void* p);
 /* Replaces the macroblock loop of compress_to_awi (awi.c:85-128): colour transform
  * (color.c:14-36), 4:2:0 pick (color.c:69-86), DCT + quantise + scan (dct.c:26-53,
  * 109-126,159-169), run-length coding (rle.c:52-110), bit packing (bitrw.c:9-43) and
- * the six DC predictors (awi.c:91-92).  *payload is malloc'd by the library. */
+ * the six DC predictors (awi.c:91-92).  *payload is allocated by the library (page-locked); release it with
+ * gpu_codec_free. */
 bool gpu_codec_encode_bgr(const uint8_t* bmp_rows, int width, int height, int row_stride,
                           uint8_t** payload, size_t* payload_len);
 
 /* Image-parallel batch of equally sized frames (whole frames per GPU, predictors reset
- * per frame — n independent compress_to_awi calls).  payloads[i] is malloc'd. */
+ * per frame — n independent compress_to_awi calls).  payloads[i] is allocated by the library, one gpu_codec_free each. */
 bool gpu_codec_encode_batch_bgr(const uint8_t* const* frames, int n_frames, int width, int height,
                                 int row_stride, uint8_t** payloads, size_t* payload_lens);
 
 /* Replaces the macroblock loop of decompress_awi (awi.c:175-217) with the BMP sink's
  * layout (bmp.c:222-260): read_and_rle_decode_chunk (rle.c:113-170), inverse scan and
  * dequantise (dct.c:128-145,171-181), IDCT (dct.c:55-81), 4:2:0 replicate (color.c:88-105),
- * inverse colour (color.c:45-67), crop.  Row padding bytes are left untouched. */
+ * inverse colour (color.c:45-67), crop.  Row padding bytes are left untouched.  `len` is the exact payload length
+ * (file size - 16): the chunks must end on its last byte (the reference would ignore trailing bytes). */
 bool gpu_codec_decode_to_bgr(const uint8_t* payload, size_t len, int width, int height,
                              uint8_t* bmp_rows, int row_stride);
 
