@@ -42,11 +42,15 @@ constexpr int REC_MB = REC_MB_N;     // macroblocks per reconstruct CTA
 constexpr int REC_TPB = 8 / REC_ROWS;     // IDCT threads per 8x8 block
 constexpr int REC_THREADS = REC_MB * 6 * REC_TPB;
 
-// map entry: bit 63 valid | bits 8..47 chunk count | bits 0..7 exit offset into the next node
+// map entry: bit 63 valid | bits 8..47 chunk count | bits 0..7 exit offset into the next node.
+// Without bit 63 the chain died on the way (no legal chunk where one had to start, or the payload ended inside
+// one); the count then says how many whole chunks it got through, which is what decides whether a stream with
+// bytes after its last chunk is still complete (the reference stops reading after the last chunk, awi.c:184-217).
 constexpr unsigned long long ENT_OK = 1ull << 63;
 __device__ __forceinline__ unsigned long long ent_make(unsigned long long cnt, int exit) {
     return ENT_OK | (cnt << 8) | (unsigned long long) exit;
 }
+__device__ __forceinline__ unsigned long long ent_dead(unsigned long long cnt) { return cnt << 8; }
 __device__ __forceinline__ unsigned long long ent_cnt(unsigned long long e) { return (e >> 8) & ((1ull << 40) - 1); }
 __device__ __forceinline__ int ent_exit(unsigned long long e) { return (int) (e & 0xff); }
 
@@ -157,16 +161,17 @@ __global__ void __launch_bounds__(256) dec_scan_segments(const uint8_t* __restri
     // entry offset -> (exit offset into the next segment, chunks passed) for each of the 184 possible entry
     // offsets, by pointer jumping over the candidates: jump[i] = (where the chain from candidate i has got to,
     // chunks counted), one 32-bit word each so a pair is always read consistently; 10 doublings cover the
-    // longest chain (2048/3 chunks).  In-place updates may see a neighbour's old or new word: both are valid jumps.
+    // longest chain (2048/3 chunks).  In-place updates may see a neighbour's old or new word: both are valid jumps
+    // (a word is either (live index, chunks to get there) or final).
     const long long remain = (long long) (P - seg_start);           // bytes of payload from seg_start on
     const int lim = remain < SEG ? (int) remain : SEG;              // in the last segment a legal chain ends exactly at lim
     for (int i = tid; i < n_cand; i += 256) {
-        unsigned w = DEAD;
+        unsigned w = DEAD;                                           // (count 0: no chunk starts here)
         const int l = cand_len[i], p = cand_pos[i];
         if (l != 0 && p < lim) {
             const int q = p + l;                                     // q <= lim in the last segment (longer chunks were zeroed)
             const unsigned to = q < lim ? (unsigned) idx[q] : EXITED + (unsigned) (q - lim);      // NONE == DEAD: the chain stops at q
-            w = to == DEAD ? DEAD : (to | (1u << 16));
+            w = to | (1u << 16);                                     // one chunk passed, even if nothing can follow it
         }
         jump[i] = w;
     }
@@ -177,7 +182,7 @@ __global__ void __launch_bounds__(256) dec_scan_segments(const uint8_t* __restri
             const unsigned w = jump[i], n = w & 0xffffu;
             if (n < EXITED) {
                 const unsigned w2 = jump[n], n2 = w2 & 0xffffu;
-                jump[i] = n2 == DEAD ? DEAD : (n2 | ((w >> 16) + (w2 >> 16)) << 16);
+                jump[i] = n2 | ((w >> 16) + (w2 >> 16)) << 16;       // a dead end keeps the number of chunks passed
                 moved = 1;
             }
         }
@@ -191,6 +196,7 @@ __global__ void __launch_bounds__(256) dec_scan_segments(const uint8_t* __restri
         } else if (e < lim && idx[e] != NONE) {
             const unsigned w = jump[idx[e]], n = w & 0xffffu;
             if (n != DEAD && n >= EXITED) r = ent_make(w >> 16, remain <= SEG ? 0 : (int) (n - EXITED));
+            else if (n == DEAD) r = ent_dead(w >> 16);
         }
         table[(unsigned long long) blockIdx.x * MAXCH + tid] = r;
     }
@@ -218,11 +224,12 @@ __global__ void __launch_bounds__(192) dec_compose(const unsigned long long* __r
         pre[(c0 + c) * MAXCH + threadIdx.x] = ok ? ent_make(cnt, e) : 0ull;
         if (ok) {
             unsigned long long t = child_tab[c * MAXCH + e];
+            cnt += ent_cnt(t);                                       // (a dying child still counts the chunks it got through)
             if (!(t & ENT_OK)) ok = false;
-            else { cnt += ent_cnt(t); e = ent_exit(t); }
+            else e = ent_exit(t);
         }
     }
-    out[(long long) blockIdx.x * MAXCH + threadIdx.x] = ok ? ent_make(cnt, e) : 0ull;
+    out[(long long) blockIdx.x * MAXCH + threadIdx.x] = ok ? ent_make(cnt, e) : ent_dead(cnt);
 }
 
 // ---------------------------------------------------------------- 3: expand
@@ -255,7 +262,8 @@ __global__ void __launch_bounds__(256) dec_root_expand(const unsigned long long*
     if (threadIdx.x == 0) {
         const unsigned long long t = top_table[0];
         NodeState st; st.first_chunk = 0; st.entry = 0; st.ok = 1;
-        if (!(t & ENT_OK) || ent_cnt(t) != expect_chunks) { st.ok = 0; atomicOr(err, 2u); }
+        // complete = the chain from byte 0 gets through at least the expected number of chunks, whatever follows them
+        if (ent_cnt(t) < expect_chunks) { st.ok = 0; atomicOr(err, 2u); }
         T.state[T.levels - 1][0] = st;
     }
     __syncthreads();
@@ -302,13 +310,17 @@ __global__ void __launch_bounds__(256) dec_emit_offsets(const uint8_t* __restric
     const uint8_t* L = Ls + threadIdx.x * SEG;
     int pos = st.entry;
     unsigned long long c = st.first_chunk;
+    bool alive = true;
     while (pos < lim && c < n_chunks) {
-        chunk_off[c++] = (uint32_t) (seg_start + pos);
+        chunk_off[c] = (uint32_t) (seg_start + pos);
         const int l = L[pos];
-        if (l == 0) break;
+        if (l == 0) { alive = false; break; }
         pos += l;
+        c++;
     }
-    if (remain <= SEG && c == n_chunks) chunk_off[n_chunks] = (uint32_t) P;
+    // where the last chunk ends (the payload end, or the first byte the reference would not read); the segment the
+    // last chunk runs into may write the same value again
+    if (alive && c == n_chunks) chunk_off[n_chunks] = (uint32_t) (seg_start + pos);
 }
 
 // ---------------------------------------------------------------- 5: DC scan

@@ -89,8 +89,8 @@ bool gpu_codec_encode_batch_bgr(const uint8_t* const* frames, int n_frames, int 
 /* Replaces the macroblock loop of decompress_awi (awi.c:175-217) with the BMP sink's
  * layout (bmp.c:222-260): read_and_rle_decode_chunk (rle.c:113-170), inverse scan and
  * dequantise (dct.c:128-145,171-181), IDCT (dct.c:55-81), 4:2:0 replicate (color.c:88-105),
- * inverse colour (color.c:45-67), crop.  Row padding bytes are left untouched.  `len` is the exact payload length
- * (file size - 16): the chunks must end on its last byte (the reference would ignore trailing bytes). */
+ * inverse colour (color.c:45-67), crop.  Row padding bytes are left untouched.  The payload must hold all
+ * 6 x macroblocks chunks; bytes after the last chunk are ignored, as the reference does. */
 bool gpu_codec_decode_to_bgr(const uint8_t* payload, size_t len, int width, int height,
                              uint8_t* bmp_rows, int row_stride);
 
