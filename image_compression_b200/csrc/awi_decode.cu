@@ -24,6 +24,7 @@
 #include <stdint.h>
 #include "codec_math.cuh"
 #include "awi_kernels.h"
+#include <mutex>
 
 namespace awi {
 
@@ -470,10 +471,16 @@ __global__ void __launch_bounds__(REC_THREADS) dec_reconstruct(DecParams P, cons
     if (*reinterpret_cast<volatile unsigned int*>(err) != 0) return;          // an earlier stage rejected the stream
 
     // the tile's chunks are contiguous in the stream: [b0, b1)
-    const uint32_t b0 = chunk_off[chunk0], b1 = chunk_off[chunk0 + n_ch];
+    const uint32_t b0 = chunk_off[chunk0], b1_raw = chunk_off[chunk0 + n_ch];
     uint32_t my_off = 0;
     int my_dc = 0;
     if (tid < n_ch) { my_off = chunk_off[chunk0 + tid]; my_dc = dcabs[chunk0 + tid]; }      // in flight during staging
+    uint32_t b1 = b1_raw;
+    // With the encoder's side-info the end of the last chunk is not known, only the end of the payload: whatever
+    // follows the last chunk is ignored (as the reference does, awi.c:184-217), so the last tile's slice is cut
+    // to the longest it can legally be.  Anywhere else an over-long slice means inconsistent offsets.
+    const bool last_tile = chunk0 + n_ch == (long long) P.mbw * P.mbh * 6;
+    if (last_tile && b1 >= b0 && b1 - b0 > (uint32_t) (REC_MB * 6 * MAXCH)) b1 = b0 + (uint32_t) (REC_MB * 6 * MAXCH);
     if (b1 < b0 || b1 > P.payload_len || b1 - b0 > (uint32_t) (REC_MB * 6 * MAXCH)) { if (tid == 0) atomicOr(err, 4u); return; }
     if (tid < 64) {
         const double c = (double) __uint_as_float(cos_bits_rt(tid));          // cos_table[x = tid>>3][v = tid&7]
@@ -645,6 +652,8 @@ __global__ void __launch_bounds__(REC_THREADS) dec_reconstruct(DecParams P, cons
     }
 }
 
+__global__ void dec_set_word(uint32_t* p, uint32_t v) { *p = v; }
+
 // ---------------------------------------------------------------- host side
 static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
@@ -696,6 +705,8 @@ cudaError_t launch_decode(const DecParams& P, void* workspace, size_t workspace_
     if (workspace_bytes < Lo.total) return cudaErrorInvalidValue;
     {   // kernels with more than 48 KB of dynamic shared memory have to opt in, once per device
         static bool attr_set[64] = { false };
+        static std::mutex attr_mu;                   // contexts of several devices may launch from different host threads
+        std::lock_guard<std::mutex> attr_lock(attr_mu);
         int dev = 0;
         cudaGetDevice(&dev);
         if (dev < 0 || dev >= 64 || !attr_set[dev]) {
@@ -733,9 +744,7 @@ cudaError_t launch_decode(const DecParams& P, void* workspace, size_t workspace_
     } else {
         cudaError_t e = cudaMemcpyAsync(chunk_off, chunk_off_in, (size_t) n_chunks * 4, cudaMemcpyDeviceToDevice, stream);
         if (e != cudaSuccess) return e;
-        uint32_t end = (uint32_t) P.payload_len;
-        e = cudaMemcpyAsync(chunk_off + n_chunks, &end, 4, cudaMemcpyHostToDevice, stream);
-        if (e != cudaSuccess) return e;
+        dec_set_word<<<1, 1, 0, stream>>>(chunk_off + n_chunks, (uint32_t) P.payload_len);     // the value rides in the launch, no host buffer to outlive
     }
 
     if (!reuse_index) {

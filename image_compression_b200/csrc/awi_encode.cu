@@ -31,6 +31,7 @@
 #include <stdint.h>
 #include "codec_math.cuh"
 #include "awi_kernels.h"
+#include <mutex>
 #include <type_traits>
 
 namespace awi {
@@ -778,10 +779,12 @@ __global__ void __launch_bounds__(256) enc_gather_tiles(const uint8_t* __restric
                                                         uint8_t* __restrict__ out, const unsigned long long* __restrict__ out_len,
                                                         unsigned long long out_cap, uint32_t* __restrict__ chunk_off,
                                                         int tiles_per_frame, int chunks_per_frame,
-                                                        unsigned long long* __restrict__ frame_off) {
+                                                        unsigned long long* __restrict__ frame_off,
+                                                        unsigned long long stage_cap_units) {
     const int tile = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (tile >= n_tiles || *out_len > out_cap) return;
     const uint2 info = tile_info[tile];
+    if ((unsigned long long) info.x + ((info.y + 15u) >> 4) > stage_cap_units) return;   // never staged (err bit 0 is already set)
     const unsigned long long off = tile_off[tile];
     const uint32_t total = info.y;
     const uint8_t* src = stage + (unsigned long long) info.x * 16;
@@ -821,7 +824,8 @@ __global__ void __launch_bounds__(256) enc_scan_gather_tiles(const uint8_t* __re
                                                              unsigned long long out_cap, unsigned int* err,
                                                              unsigned int* __restrict__ stage_cursor,
                                                              uint32_t* __restrict__ chunk_off, int tiles_per_frame,
-                                                             int chunks_per_frame, unsigned long long* __restrict__ frame_off) {
+                                                             int chunks_per_frame, unsigned long long* __restrict__ frame_off,
+                                                             unsigned long long stage_cap_units) {
     __shared__ unsigned long long wsum[8];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int first = blockIdx.x * 8;
@@ -863,7 +867,12 @@ __global__ void __launch_bounds__(256) enc_scan_gather_tiles(const uint8_t* __re
         for (int i = lane; i < TILE_MB * 6 && c_in + i < chunks_per_frame; i += 32) chunk_off[c0 + i] += (uint32_t) off;
     }
     if (!fits) return;                                       // (offsets only grow: the last tile reports it)
-    const uint8_t* src = stage + (unsigned long long) tile_info[tile].x * 16;
+    // Tiles are staged in completion order, so a tile from the front of the frame can have reserved room
+    // behind the end of the staging buffer (and then staged nothing) while its payload offset still fits:
+    // it must not be copied from there.  The encode kernel has raised err bit 0 for it already.
+    const unsigned long long at = tile_info[tile].x;
+    if (at + ((total + 15u) >> 4) > stage_cap_units) return;
+    const uint8_t* src = stage + at * 16;
     uint8_t* dst = out + off;
     const uint32_t head = min(total, (uint32_t) ((4 - (reinterpret_cast<uintptr_t>(dst) & 3)) & 3));
     if (lane < head) dst[lane] = src[lane];
@@ -881,17 +890,20 @@ size_t enc_smem_bytes() { return sizeof(EncSmem); }
 
 cudaError_t launch_encode(const EncParams& P, int n_tiles, cudaStream_t stream) {
     static bool attr_set[64] = { false };
+    static std::mutex attr_mu;                       // contexts of several devices may launch from different host threads
     int dev = 0;
     cudaGetDevice(&dev);
-    if (dev < 64 && !attr_set[dev]) {
+    std::unique_lock<std::mutex> attr_lock(attr_mu);
+    if (dev < 0 || dev >= 64 || !attr_set[dev]) {
         cudaError_t e = cudaFuncSetAttribute(awi_encode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              (int) sizeof(EncSmem));
         if (e != cudaSuccess) return e;
         e = cudaFuncSetAttribute(awi_encode_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
                                  cudaSharedmemCarveoutMaxShared);
         if (e != cudaSuccess) return e;
-        attr_set[dev] = true;
+        if (dev >= 0 && dev < 64) attr_set[dev] = true;
     }
+    attr_lock.unlock();
     EncParams Q = P;
     Q.n_tiles = n_tiles;
     if (Q.compact_cap <= 0 || Q.compact_cap > COMPACT_CAP) Q.compact_cap = COMPACT_CAP;
@@ -901,13 +913,14 @@ cudaError_t launch_encode(const EncParams& P, int n_tiles, cudaStream_t stream) 
         if (n_tiles <= ENC_FUSED_MAX_TILES) {
             enc_scan_gather_tiles<<<(n_tiles + 7) / 8, 256, 0, stream>>>(P.stage, P.tile_info, n_tiles, P.out, P.out_len, P.out_len_user,
                                                                          P.chain_in, P.chain_out, P.out_cap, P.err, P.stage_cursor,
-                                                                         P.chunk_off, Q.tiles_per_frame, (P.mb1 - P.mb0) * 6, P.frame_off);
+                                                                         P.chunk_off, Q.tiles_per_frame, (P.mb1 - P.mb0) * 6, P.frame_off,
+                                                                         P.stage_cap_units);
         } else {
             enc_scan_tiles<<<1, 1024, 0, stream>>>(P.tile_info, n_tiles, P.tile_off, P.out_len, P.chain_in, P.chain_out, P.out_cap, P.err,
                                                    P.out_len_user, P.stage_cursor);
             enc_gather_tiles<<<(n_tiles + 7) / 8, 256, 0, stream>>>(P.stage, P.tile_info, P.tile_off, n_tiles, P.out, P.out_len,
                                                                      P.out_cap, P.chunk_off, Q.tiles_per_frame,
-                                                                     (P.mb1 - P.mb0) * 6, P.frame_off);
+                                                                     (P.mb1 - P.mb0) * 6, P.frame_off, P.stage_cap_units);
         }
     }
     return cudaGetLastError();

@@ -426,7 +426,7 @@ bool encode_dev_impl(Ctx* c, const uint8_t* d_rows, int width, int height, long 
     if (!ensure(c->enc_ws, ws_bytes) || !ensure(c->enc_stage, stage_bytes)) return false;
     // the staging cursor must be zero when a launch starts: once here for a fresh buffer, afterwards the scan
     // kernel of every launch leaves it at zero (one operation less per call)
-    if (c->enc_ws.bytes != ws_before) CU(cudaMemset(c->enc_ws.p, 0, ENC_WS_HEADER));
+    if (c->enc_ws.bytes != ws_before) CU(cudaMemsetAsync(c->enc_ws.p, 0, ENC_WS_HEADER, st));      // ordered with the kernels that follow on `st`
 
     awi::EncParams P{};
     // address of bottom-up row 0 of the full frame, had the whole frame been resident
@@ -502,11 +502,22 @@ bool check_err(Ctx* c, cudaStream_t st, const char* what) {
     CU(cudaStreamSynchronize(st));
     const unsigned int e = *h_err;
     if (e) {
-        CU(cudaMemset(c->d_err, 0, 4));
+        CU(cudaMemsetAsync(c->d_err, 0, 4, st));      // on the stream the flags came back on: cannot wipe a later call's flag
+        CU(cudaStreamSynchronize(st));
         return fail("%s: device reported%s%s%s", what, (e & 1) ? " [payload buffer too small]" : "",
                     (e & 2) ? " [malformed stream: chunk boundaries]" : "", (e & 4) ? " [malformed stream: chunk body]" : "");
     }
     return true;
+}
+
+// Failure paths: nothing may still be reading the caller's pixels or writing into a block that is about to be
+// handed back when a host entry point returns, so every stream of the context is drained first.
+void drain(Ctx* c) {
+    cudaSetDevice(c->dev);
+    cudaStreamSynchronize(c->copy_stream);
+    cudaStreamSynchronize(c->stream);
+    cudaStreamSynchronize(c->back_stream);
+    cudaGetLastError();
 }
 
 // rows of stripe g of G over mbh macroblock rows
@@ -714,7 +725,7 @@ static bool encode_frame_streamed(Ctx* c, const uint8_t* bmp_rows, int width, in
                                   uint8_t** payload, size_t* payload_len) {
     const int mbh = (height + 15) / 16;
     int n_sub = 1;
-    if (!encode_stripe_async(c, bmp_rows, width, height, row_stride, 0, mbh, &n_sub)) return false;
+    if (!encode_stripe_async(c, bmp_rows, width, height, row_stride, 0, mbh, &n_sub)) { drain(c); return false; }
     uint8_t* buf = nullptr;
     size_t cap = 0, prev = 0;
     bool overflow = false, ok = true;
@@ -746,7 +757,7 @@ static bool encode_frame_streamed(Ctx* c, const uint8_t* bmp_rows, int width, in
         if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
         if (e != cudaSuccess) ok = fail("encode: D2H failed: %s", cudaGetErrorString(e));
     }
-    if (!ok) { if (buf) pool_put(buf); return false; }
+    if (!ok) { drain(c); if (buf) pool_put(buf); return false; }
     *payload = buf;
     *payload_len = total;
     return true;
@@ -769,13 +780,19 @@ bool gpu_codec_encode_bgr(const uint8_t* bmp_rows, int width, int height, int ro
     for (int g = 0; g < G; g++) {
         int r0, r1;
         stripe_rows(mbh, g, G, r0, r1);
-        if (!encode_stripe_async(g_ctx[g], bmp_rows, width, height, row_stride, r0, r1)) return false;
+        if (!encode_stripe_async(g_ctx[g], bmp_rows, width, height, row_stride, r0, r1)) {
+            for (int k = 0; k <= g; k++) drain(g_ctx[k]);
+            return false;
+        }
     }
     // phase 2: exclusive prefix sum of the per-stripe byte lengths, stitch (byte seams)
     size_t total = 0;
     std::vector<size_t> off(G), len(G);
     for (int g = 0; g < G; g++) {
-        if (!check_err(g_ctx[g], g_ctx[g]->stream, "encode")) return false;
+        if (!check_err(g_ctx[g], g_ctx[g]->stream, "encode")) {
+            for (int k = 0; k < G; k++) drain(g_ctx[k]);
+            return false;
+        }
         off[g] = total;
         len[g] = (size_t) *g_ctx[g]->h_len;
         total += len[g];
@@ -786,12 +803,20 @@ bool gpu_codec_encode_bgr(const uint8_t* bmp_rows, int width, int height, int ro
         Ctx* c = g_ctx[g];
         cudaSetDevice(c->dev);
         cudaError_t e = cudaMemcpyAsync(buf + off[g], c->out.p, len[g], cudaMemcpyDeviceToHost, c->stream);
-        if (e != cudaSuccess) { pool_put(buf); return fail("encode: D2H failed: %s", cudaGetErrorString(e)); }
+        if (e != cudaSuccess) {
+            for (int k = 0; k < G; k++) drain(g_ctx[k]);
+            pool_put(buf);
+            return fail("encode: D2H failed: %s", cudaGetErrorString(e));
+        }
     }
     for (int g = 0; g < G; g++) {
         cudaSetDevice(g_ctx[g]->dev);
         cudaError_t e = cudaStreamSynchronize(g_ctx[g]->stream);
-        if (e != cudaSuccess) { pool_put(buf); return fail("encode: sync failed: %s", cudaGetErrorString(e)); }
+        if (e != cudaSuccess) {
+            for (int k = 0; k < G; k++) drain(g_ctx[k]);
+            pool_put(buf);
+            return fail("encode: sync failed: %s", cudaGetErrorString(e));
+        }
     }
     *payload = buf;
     *payload_len = total;
@@ -983,6 +1008,7 @@ bool gpu_codec_decode_to_rgb24(const uint8_t* payload, size_t len, int width, in
 namespace {
 
 constexpr int NOALLOC_MAX_TILES = 2097152 / awi::ENC_TILE_MB;   // 65536 tiles = 2,097,152 macroblocks, e.g. up to 23168 x 23168 pixels
+static_assert(awi::ENC_TILE_MB == 32, "include/gpu_codec.h, DESIGN.md and INTEGRATION.md quote 65536 tiles / 512 KB + 256 B for 32-macroblock tiles");
 constexpr size_t NOALLOC_HEADER = 256;            // [0,8) spare, [8,12) tile ticket
 static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_HEADER + (size_t) NOALLOC_MAX_TILES * 8];
 

@@ -143,9 +143,13 @@ bool gpu_codec_encode_batch_bgr_dev(int ctx, const uint8_t* d_frames, int n_fram
  *     first call before starting any stream capture;
  *   - all calls on one device share the array: two calls whose kernels overlap on the
  *     GPU (different streams, no ordering) corrupt each other; order them;
- *   - d_payload_len (8 bytes) receives the payload length, d_status (4 bytes) 0 on
- *     success or bit 0 set when payload_cap was too small (then nothing was written).
- *     Both are written on `stream`; read them after synchronising it. */
+ *   - d_payload_len (8 bytes) always receives the length the payload needs; d_status (4 bytes)
+ *     is 0 on success, or has bit 0 set when payload_cap was smaller than that length.  In that
+ *     case the tiles that still fitted have been written, so the contents of d_payload are
+ *     unspecified: retry with a buffer of at least *d_payload_len bytes
+ *     (gpu_codec_max_payload_bytes always suffices).  Both words are written on `stream`; read
+ *     them after synchronising it.
+ * The sizes above are for the library as shipped (32 macroblocks per tile); the source asserts it. */
 bool gpu_codec_encode_bgr_dev_noalloc(const uint8_t* d_rows, int width, int height, long long row_stride,
                                       uint8_t* d_payload, size_t payload_cap, uint64_t* d_payload_len,
                                       uint32_t* d_status, void* stream);
@@ -163,7 +167,10 @@ bool gpu_codec_decode_dev(int ctx, const uint8_t* d_payload, size_t len, int wid
  * flagged an error (payload_cap too small, malformed stream, CUDA error). */
 bool gpu_codec_sync_check(int ctx, void* stream);
 
-/* ------------------------------------------------------------------ synthetic frames + self-tests */
+/* ------------------------------------------------------------------ synthetic frames + self-tests
+ * Everything below this line serves the repository's own tests and bench (synthetic inputs, exhaustive colour
+ * check, a knob that forces a rarely taken write path).  It is NOT part of the stable drop-in surface: a host
+ * that binds the codec needs none of it, and names or behaviour may change between versions. */
 
 /* Fill d_rows (bottom-up BGR, row_stride apart) with an integer-only synthetic frame;
  * kind 0 = noise, 1 = photo-like, 2 = flat 144 (identical to image_compression_b200/synth.py). */
@@ -176,7 +183,8 @@ bool gpu_codec_selftest_colour_dev(int ctx, const uint8_t* d_in, size_t n, int i
 
 /* Test hook: pretend the encoder's per-tile shared-memory buffer holds only `bytes` (0 restores the real
  * 12 KB), which forces the chunk-by-chunk write path that otherwise needs > 64 bytes per chunk on average
- * across a whole tile.  Results are unaffected.  No counterpart in the reference. */
+ * across a whole tile.  Results are unaffected.  No counterpart in the reference.  Process-wide and not
+ * synchronised: set it only while no encode call is running (tests only). */
 void gpu_codec_selftest_tile_buffer(int bytes);
 
 #ifdef __cplusplus

@@ -75,6 +75,9 @@ class Port:
                                              _u8p, C.c_size_t, _i8p, _u32p]
         L.awi_oracle_decode.restype = C.c_long
         L.awi_oracle_decode.argtypes = [_u8p, C.c_size_t, C.c_int, C.c_int, _u8p, C.c_size_t, C.c_int, _u32p]
+        L.awi_oracle_decode_rows.restype = C.c_long
+        L.awi_oracle_decode_rows.argtypes = [_u8p, C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_int, C.c_size_t, _i32p,
+                                             C.c_void_p, C.c_size_t, C.c_int, _u32p]
         L.awi_oracle_rle.restype = C.c_int
         L.awi_oracle_rle.argtypes = [_i32p, C.c_int, _u8p]
         L.awi_oracle_unrle.restype = C.c_int
@@ -124,6 +127,17 @@ class Port:
         if used < 0:
             raise ValueError("malformed AWI payload")
         return (dst, used, off) if want_offsets else (dst, used)
+
+    def decode_rows(self, payload: np.ndarray, w: int, h: int, mb_row0: int, mb_row1: int, start: int, pred,
+                    dst: np.ndarray, stride: int, rgb_topdown=False) -> int:
+        """Macroblock rows [mb_row0, mb_row1) from byte `start` with the six predictors `pred` as they stand
+        there, into the full-frame buffer `dst` (only the band is written).  Returns the offset after the band."""
+        pr = np.ascontiguousarray(pred, np.int32)
+        end = self.lib.awi_oracle_decode_rows(_ptr(payload, _u8p), payload.size, w, h, mb_row0, mb_row1, start,
+                                              _ptr(pr, _i32p), dst.ctypes.data, stride, 1 if rgb_topdown else 0, None)
+        if end < 0:
+            raise ValueError("malformed AWI payload")
+        return int(end)
 
     # -- stages ------------------------------------------------------------
     def transform(self, px: np.ndarray, chroma: int) -> np.ndarray:

@@ -347,18 +347,24 @@ size_t awi_oracle_encode_bgr(const uint8_t* rows, int w, int h, size_t stride,
 
 /* awi.c:175-217 + the two sinks: rgb_topdown == 0 -> bottom-up BGR rows `stride`
  * apart (bmp.c:222-260 and the flush order of :191-220), else packed top-down
- * RGB24 with pitch 3w (bmp.c:291-320).  Returns payload bytes consumed, -1 on a
- * malformed stream. */
-long awi_oracle_decode(const uint8_t* payload, size_t n, int w, int h,
-                       uint8_t* dst, size_t stride, int rgb_topdown, uint32_t* chunk_off) {
-    int mbw = (w + 15) / 16, mbh = (h + 15) / 16;
+ * RGB24 with pitch 3w (bmp.c:291-320).  Macroblock rows [mb_row0, mb_row1) only, reading from byte
+ * `start` of the payload with the six predictors as they stand there (`pred_in`, NULL = zeros: the
+ * frame start) — so that tests can spread a large frame over host threads; `dst` is the address of
+ * the FULL frame's first byte, only the band's pixels are written.  Returns the byte offset after
+ * the band's last chunk, -1 on a malformed stream. */
+long awi_oracle_decode_rows(const uint8_t* payload, size_t n, int w, int h, int mb_row0, int mb_row1,
+                            size_t start, const int* pred_in,
+                            uint8_t* dst, size_t stride, int rgb_topdown, uint32_t* chunk_off) {
+    int mbw = (w + 15) / 16;
     int pred[6] = { 0, 0, 0, 0, 0, 0 };
-    size_t pos = 0, ci = 0;
-    for (int my = 0; my < mbh; my++) {
+    if (pred_in) for (int k = 0; k < 6; k++) pred[k] = pred_in[k];
+    size_t pos = start, ci = 0;
+    for (int my = mb_row0; my < mb_row1; my++) {
         for (int mx = 0; mx < mbw; mx++) {
             uint8_t blk[6][64]; int chunk[64];
             for (int k = 0; k < 6; k++, ci++) {
                 if (chunk_off) chunk_off[ci] = (uint32_t) pos;
+                if (pos > n) return -1;
                 int used = awi_oracle_unrle(payload + pos, n - pos, pred[k], chunk);
                 if (used < 0) return -1;
                 pos += (size_t) used;
@@ -388,4 +394,9 @@ long awi_oracle_decode(const uint8_t* payload, size_t n, int w, int h,
         }
     }
     return (long) pos;
+}
+
+long awi_oracle_decode(const uint8_t* payload, size_t n, int w, int h,
+                       uint8_t* dst, size_t stride, int rgb_topdown, uint32_t* chunk_off) {
+    return awi_oracle_decode_rows(payload, n, w, h, 0, (h + 15) / 16, 0, NULL, dst, stride, rgb_topdown, chunk_off);
 }

@@ -1,7 +1,7 @@
-"""GPU (-m gpu): BASELINE.json's full sizes.  The oracle is too slow to restate these
-whole, so parity rests on (a) the oracle on a band of macroblock rows, (b) size-independent
-properties: stripes == whole, discovered chunk offsets == encoder offsets, decode of the
-device payload == oracle decode on a band, payload length == last offset + last chunk."""
+"""GPU (-m gpu): BASELINE.json's full sizes, whole frames against the oracle.  One oracle thread would
+take minutes on 16384x16384, so the frame is cut into bands of macroblock rows that run on all host
+threads (tests/_bands.py; the bands are exact because only six DC predictors cross a band seam); on top
+of that the size-independent properties: stripes == whole, discovered chunk offsets == encoder offsets."""
 import numpy as np
 import pytest
 
@@ -43,9 +43,14 @@ def test_4k_and_1080p_whole_frame_vs_oracle(gpu, port, cfg):
 
 
 @pytest.mark.parametrize("kind", ["photo", "noise"])
-def test_16k_properties(gpu, port, kind):
-    """config[2]: 16384x16384.  Oracle on two bands; 8-way stripes == whole; decode round trip."""
+def test_16k_whole_frame_vs_oracle(gpu, port, ref, kind):
+    """config[2]: 16384x16384, EVERY byte against the oracle (bands of macroblock rows on the host's threads,
+    tests/_bands.py): payload, chunk offsets, decoded pixels; photo-like content also against the unmodified
+    reference build where it travelled.  Plus the size-independent properties: 8-way stripes == whole,
+    discovered chunk offsets == encoder offsets."""
     import torch
+    import oracle
+    import _bands
     w = h = 16384
     stride = 3 * w
     t = torch.empty(h * stride, dtype=torch.uint8, device="cuda")
@@ -53,18 +58,16 @@ def test_16k_properties(gpu, port, kind):
     p, off = _encode(gpu, t, w, h, stride)
     mbw, mbh = w // 16, h // 16
     offs = off.cpu().numpy().view(np.uint32).astype(np.int64)
-    assert (np.diff(offs) >= 3).all() and (np.diff(offs) <= 121).all() and offs[0] == 0
-    assert 3 <= p.numel() - offs[-1] <= 121
-    # oracle on two bands of macroblock rows (the second one starts at a seam)
-    for r0, r1 in ((0, 2), (511, 514)):
-        y0, y1 = stripes.stripe_window(h, r0, r1)
-        b0, b1 = stripes.window_byte_range(h, stride, y0, y1)
-        # hand the oracle a virtual full frame: only the window is populated
-        win = t[b0:b1].cpu().numpy()
-        want = port_encode_window(port, win, w, h, stride, y0, y1, r0, r1)
-        lo = offs[r0 * mbw * 6]
-        hi = offs[r1 * mbw * 6] if r1 < mbh else p.numel()
-        assert p[lo:hi].cpu().numpy().tobytes() == want.tobytes(), (kind, r0)
+    rows = t.cpu().numpy()
+    got = p.cpu().numpy()
+    # whole frame, restatement: bytes and chunk boundaries
+    want, lens = _bands.port_encode_frame(port, rows, w, h, stride)
+    assert got.size == want.size and got.tobytes() == want.tobytes(), kind
+    assert (offs == np.concatenate([[0], np.cumsum(lens.astype(np.int64))])[:-1]).all()
+    # whole frame, the reference's own compress_to_awi (the unmodified sources)
+    if ref is not None and kind == "photo":
+        _bands.ref_check_frame(ref, oracle, rows, w, h, stride, got, offs)
+    del rows
     # 8-way stripes, each from its own window only
     parts = []
     for r0, r1 in stripes.stripe_rows(mbh, 8):
@@ -74,58 +77,50 @@ def test_16k_properties(gpu, port, kind):
         parts.append(seg)
     assert torch.equal(torch.cat(parts), p)
     del parts
-    # decode: discovery finds the encoder's offsets, pixels agree with side-info decode
+    # decode: stand-alone (boundary discovery) and with the encoder's offsets, both against the oracle's pixels
+    want_px = _bands.port_decode_frame(port, want, lens, w, h, stride)
     dst = torch.zeros(h * stride, dtype=torch.uint8, device="cuda")
     gpu.decode_dev(0, p, p.numel(), w, h, dst, stride)
     gpu.sync_check(0)
-    dst2 = torch.zeros(h * stride, dtype=torch.uint8, device="cuda")
-    gpu.decode_dev(0, p, p.numel(), w, h, dst2, stride, chunk_off=off)
+    assert dst.cpu().numpy().tobytes() == want_px.tobytes(), kind
+    dst.zero_()
+    gpu.decode_dev(0, p, p.numel(), w, h, dst, stride, chunk_off=off)
     gpu.sync_check(0)
-    assert torch.equal(dst, dst2)
-    # oracle decode of the first two macroblock rows (predictors start at zero there)
-    head = p[: offs[2 * mbw * 6]].cpu().numpy()
-    want_px, _ = port.decode(head, w, 32, stride)
-    got = dst.view(h, stride)[h - 32:].cpu().numpy()
-    assert got.tobytes() == want_px.tobytes()
+    assert dst.cpu().numpy().tobytes() == want_px.tobytes(), kind
 
 
-def port_encode_window(port, win, w, h, stride, y0, y1, r0, r1):
-    """Oracle on a window of rows: the oracle addresses rows as rows + (h-1-y)*stride, so give
-    it a base pointer shifted as if the whole frame were present (only the window is touched)."""
-    import ctypes as C
-    lib = port.lib
-    nch = (r1 - r0) * ((w + 15) // 16) * 6
-    out = np.empty(nch * 121 + 16, np.uint8)
-    base = win.ctypes.data - (h - y1) * stride
-    lib.awi_oracle_encode_rows.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_size_t, C.c_int, C.c_int,
-                                           C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p]
-    n = lib.awi_oracle_encode_rows(C.c_void_p(base), w, h, stride, r0, r1, out.ctypes.data, out.size, None, None)
-    return out[:n]
-
-
-def test_8k_decode_roundtrip(gpu, port):
-    """config[4]: 8192x8192 round-trip decode; oracle on the top band, both sinks."""
+@pytest.mark.parametrize("kind", ["photo", "noise"])
+def test_8k_decode_whole_frame_vs_oracle(gpu, port, ref, kind):
+    """config[4]: 8192x8192 round-trip decode, every pixel of both sinks against the oracle (and the encoder's
+    payload against it too, since that is what gets decoded)."""
     import torch
+    import oracle
+    import _bands
     w = h = 8192
     stride = 3 * w
     t = torch.empty(h * stride, dtype=torch.uint8, device="cuda")
-    gpu.synth_dev(0, t, w, h, stride, KIND["photo"], synth.SEED_BASE + 5, 0)
+    gpu.synth_dev(0, t, w, h, stride, KIND[kind], synth.SEED_BASE + 5, 0)
     p, off = _encode(gpu, t, w, h, stride)
+    rows = t.cpu().numpy()
+    want, lens = _bands.port_encode_frame(port, rows, w, h, stride)
+    got = p.cpu().numpy()
+    assert got.tobytes() == want.tobytes()
+    if ref is not None:
+        offs = off.cpu().numpy().view(np.uint32).astype(np.int64)
+        _bands.ref_check_frame(ref, oracle, rows, w, h, stride, got, offs)
     dst = torch.zeros(h * stride, dtype=torch.uint8, device="cuda")
     gpu.decode_dev(0, p, p.numel(), w, h, dst, stride)
     rgb = torch.zeros(h * stride, dtype=torch.uint8, device="cuda")
     gpu.decode_dev(0, p, p.numel(), w, h, rgb, stride, rgb_topdown=True)
     gpu.sync_check(0)
-    # the two sinks hold the same picture
-    a = dst.view(h, w, 3).flip(0).flip(2)
-    assert torch.equal(a, rgb.view(h, w, 3))
-    offs = off.cpu().numpy().view(np.uint32).astype(np.int64)
-    head = p[: offs[3 * (w // 16) * 6]].cpu().numpy()
-    want_px, _ = port.decode(head, w, 48, stride, rgb_topdown=True)
-    assert rgb.view(h, stride)[:48].cpu().numpy().tobytes() == want_px.tobytes()
-    # lossy but close: PSNR of the round trip stays sane
-    err = (dst.view(-1)[:: 97].float() - t.view(-1)[:: 97].float())
-    assert float((err * err).mean()) < 120.0
+    assert dst.cpu().numpy().tobytes() == _bands.port_decode_frame(port, want, lens, w, h, stride).tobytes()
+    assert rgb.cpu().numpy().tobytes() == _bands.port_decode_frame(port, want, lens, w, h, stride, True).tobytes()
+    # through the host entry points too (upload, sub-stripe pipeline, download)
+    assert gpu.decode_to_bgr(got, w, h, stride).tobytes() == dst.cpu().numpy().tobytes()
+    if kind == "photo":
+        # lossy but close: PSNR of the round trip stays sane
+        err = (dst.view(-1)[:: 97].float() - t.view(-1)[:: 97].float())
+        assert float((err * err).mean()) < 120.0
 
 
 def test_every_colour_through_the_encoder(gpu, port):

@@ -437,3 +437,58 @@ def test_corrupted_streams_agree_with_oracle(gpu, port):
         else:
             rejected += 1
     assert accepted > 0 and rejected > 0
+
+
+@pytest.mark.parametrize("size", [(2048, 1024), (4096, 4096), (8192, 4608)])     # the last one is above 4096 tiles: separate scan and gather passes
+def test_small_payload_cap_is_an_error_not_a_fault(gpu, port, size):
+    """gpu_codec_encode_bgr_dev with about half the room the payload needs: the device must report
+    "payload buffer too small" through sync_check and nothing else may break — in particular the fused
+    scan+gather pass (frames of up to 4096 tiles) must not read tiles that were never staged.  Noise
+    content: many tiles in flight, long chunks.  The context works normally afterwards."""
+    import torch
+    w, h = size
+    stride = 3 * w
+    t = torch.empty(h * stride, dtype=torch.uint8, device="cuda")
+    gpu.synth_dev(0, t, w, h, stride, KIND["noise"], synth.SEED_BASE + 11, 0)
+    full, _, _ = _dev_encode(gpu, t, w, h, stride)
+    for frac in (0.5, 0.05, 0.97):
+        cap = int(len(full) * frac)
+        guard = 4096
+        buf = torch.full((cap + guard,), 0xA5, dtype=torch.uint8, device="cuda")
+        ln = torch.zeros(1, dtype=torch.int64, device="cuda")
+        # payload_cap is what the library may write: the tensor is longer so the guard band can be checked
+        ok = gpu.load().gpu_codec_encode_bgr_dev(0, t.data_ptr(), w, h, stride, 0, h, 0, (h + 15) // 16, buf.data_ptr(), cap,
+                                                 ln.data_ptr(), None, None, torch.cuda.current_stream().cuda_stream)
+        assert ok
+        with pytest.raises(gpu.GpuCodecError, match="too small"):
+            gpu.sync_check(0)
+        assert int(ln.item()) == len(full)                       # the length the payload needs is still reported
+        assert bool((buf[cap:] == 0xA5).all().item())            # nothing past payload_cap was touched
+        gpu.sync_check(0)                                        # the flag is cleared by the failed check
+    again, _, _ = _dev_encode(gpu, t, w, h, stride)
+    assert again.tobytes() == full.tobytes()
+    if w <= 2048:
+        assert full.tobytes() == port.encode_bgr(t.cpu().numpy(), w, h, stride).tobytes()
+
+
+def test_side_info_decode_ignores_long_tail(gpu, port):
+    """Bytes after the last chunk are not read (awi.c:184-217 stops after the last macroblock), whichever
+    way the chunk boundaries are known: with the encoder's offsets as side-info the end of the last chunk is
+    not known, only the end of the buffer, and a tail longer than a whole reconstruct tile must not matter."""
+    import torch
+    w, h = 200, 120
+    stride = synth.bmp_stride(w)
+    rows = synth.frame_bgr_bottomup("photo", w, h, synth.SEED_BASE + 12)
+    t = torch.from_numpy(rows.reshape(-1)).cuda()
+    p, off, _ = _dev_encode(gpu, t, w, h, stride)
+    want = port.decode(p, w, h, stride)[0].tobytes()
+    for tail in (1, 5000, 20000):
+        rng = np.random.default_rng(tail)
+        q = np.concatenate([p, rng.integers(0, 256, tail, dtype=np.uint8)])
+        qt = torch.from_numpy(q).cuda()
+        offt = torch.from_numpy(off.view(np.int32).copy()).cuda()
+        for side in (offt, None):
+            dst = torch.zeros(h * stride, dtype=torch.uint8, device="cuda")
+            gpu.decode_dev(0, qt, qt.numel(), w, h, dst, stride, chunk_off=side)
+            gpu.sync_check(0)
+            assert dst.cpu().numpy().tobytes() == want, (tail, side is None)

@@ -184,3 +184,28 @@ def test_chunk_starts_follow_eight_zero_bits(port):
         r &= r >> 4
         if kind != "flat":
             assert ((r & 0xFF) != 0).mean() < 0.6
+
+
+def test_band_helpers_equal_whole_frame(port, ref):
+    """tests/_bands.py (the threaded whole-frame oracle runs the -m gpu tests use at 16384x16384 and
+    8192x8192) gives the same bytes, lengths and pixels as the single-threaded whole-frame calls — on ragged
+    sizes, with bands that do not divide the frame."""
+    import _bands
+    import oracle
+    from image_compression_b200 import synth
+    for kind, w, h in (("photo", 1000, 700), ("noise", 640, 427), ("photo", 2048, 1031)):
+        stride = synth.bmp_stride(w)
+        rows = synth.frame_bgr_bottomup(kind, w, h, 123)
+        want, _, wlen = port.encode_bgr(rows, w, h, stride, want_coefs=True)
+        p, lens = _bands.port_encode_frame(port, rows, w, h, stride, rows_per_band=5)
+        assert p.tobytes() == want.tobytes() and (lens == wlen).all()
+        offs = np.concatenate([[0], np.cumsum(lens.astype(np.int64))])[:-1]
+        if ref is not None:
+            _bands.ref_check_frame(ref, oracle, rows, w, h, stride, p, offs, rows_per_band=5)
+            bad = p.copy()
+            bad[offs[len(offs) // 2] + 2] ^= 0x10
+            with pytest.raises(AssertionError):
+                _bands.ref_check_frame(ref, oracle, rows, w, h, stride, bad, offs, rows_per_band=5)
+        for rgb in (False, True):
+            px = _bands.port_decode_frame(port, p, lens, w, h, stride, rgb, rows_per_band=5)
+            assert px.tobytes() == port.decode(want, w, h, stride, rgb_topdown=rgb)[0].tobytes()
