@@ -9,7 +9,8 @@ from typing import Optional, Sequence
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libgpu_codec.so")
+# GPU_CODEC_LIB: experiments only (tools/build_variant.py builds alternative kernels next to the product library)
+LIB_PATH = os.environ.get("GPU_CODEC_LIB") or os.path.join(_HERE, "libgpu_codec.so")
 
 _u8p = C.POINTER(C.c_uint8)
 

@@ -47,7 +47,10 @@ constexpr int PITCH = TILE_MB * 48 + 16;         // smem bytes per pixel row: 38
 constexpr int RAW_BYTES = 16 * PITCH;            // 24832
 constexpr int SLOT = 124;                        // staging bytes per chunk (max 121), 31 words: conflict-free
 constexpr int COMPACT_CAP = THREADS * 64;        // compacted tile lives in the (dead) coefficient buffer
-constexpr int TR_WORDS = 4 * 72;                 // per warp: 4 blocks x (8 rows x 8 floats + 8 pad)
+constexpr int TR_ROW = 80;                        // phase B transposes, per lane group: 8 rows of 8 (block A, block B) float pairs = 64 B,
+constexpr int TR_GROUP = 8 * TR_ROW;              // rows 80 B apart (20 banks: the eight 128-bit row stores of a group cover all 32 banks),
+constexpr int TR_BYTES = 4 * TR_GROUP + 2 * 64;   // groups 640 B apart, 64 B more in front of groups 1, 2 (carried on) and 3 (the two groups of a half-warp
+                                                  // read 64-byte rows 16 banks apart)
 static_assert(THREADS * SLOT <= RAW_BYTES, "chunk slots alias the raw tile");
 static_assert(THREADS == 2 * TILE_MB * 3, "loader: one fixed (macroblock, 16-byte piece) per thread, two rows per pass");
 static_assert(THREADS == TILE_MB * 6, "one thread per chunk in phases D-F");
@@ -56,7 +59,7 @@ struct __align__(16) EncSmem {
     uint8_t raw[RAW_BYTES];                      // phase A-C: pixels; phase D-F: chunk slots
     uint8_t halo[16 * 48];                       // macroblock preceding the tile
     uint32_t coef[THREADS * 16];                 // int8[64] per chunk, scan order; phase E-F: compacted tile
-    float tr[NWARPS][TR_WORDS];                  // phase B transposes
+    uint8_t tr[NWARPS][TR_BYTES];                // phase B transposes
     unsigned long long amb[THREADS];             // per chunk: natural positions to recompute
     int dc[(TILE_MB + 1) * 6];                   // quantised DCs, [0] = halo macroblock
     int halo_sum[6];
@@ -67,6 +70,8 @@ struct __align__(16) EncSmem {
     unsigned long long load_bar;                 // mbarrier the bulk copies of phase A complete on
     int tile;
 };
+
+static_assert(sizeof(EncSmem) + 1024 <= (228 * 1024) / ENC_MIN_CTAS, "ENC_MIN_CTAS tiles (+1 KB each the system keeps) must fit an SM's 228 KB");
 
 // chunk index inside the tile: 6*macroblock + type, type 0..3 = Y[i][j], 4 = Cb, 5 = Cr
 __device__ __forceinline__ int coef_word(int chunk, int word) { return chunk * 16 + word; }
@@ -189,6 +194,88 @@ __device__ __forceinline__ uint32_t div10000(uint32_t n, bool& multiple) {
     return hi >> 3;
 }
 
+// Quotient as the bit pattern of the float 2^23 + q (0x4B000000 | q): two of them side by side are a packed pair,
+// and one packed subtraction of 2^23 + 128 turns both into centred samples (float)(q - 128).
+__device__ __forceinline__ uint32_t div1000_bits(uint32_t n, uint32_t& least_low) {
+    const unsigned long long p = (unsigned long long) n * 4294968ull;
+    least_low = min(least_low, (uint32_t) p);                   // an exact multiple of 1000 shows as a low word below 2000000
+    return (uint32_t) (p >> 32) | 0x4B000000u;
+}
+// n / 10000: the quotient sits in bits 35..; the cheap test looks at the low word only (a multiple has bits
+// 0..34 below 417800, so its low word is below that too; the few non-multiples that pass are told apart by
+// the exact remainder test on the slow path).
+__device__ __forceinline__ uint32_t div10000_bits(uint32_t n, uint32_t& least_low) {
+    const unsigned long long p = (unsigned long long) n * 3435974ull;
+    least_low = min(least_low, (uint32_t) p);
+    return ((uint32_t) (p >> 32) >> 3) | 0x4B000000u;
+}
+__device__ __forceinline__ F2 centre_pair(uint32_t a, uint32_t b) {
+    return op_sub(f2_pack(__uint_as_float(a), __uint_as_float(b)), f2_splat(8388736.0f));
+}
+
+// 16 pixels (48 bytes) in 12 words -> the 16 centred luma samples of one image row of a macroblock, as
+// eight (left block, right block) pairs
+__device__ __forceinline__ void luma_row_pair(const uint32_t* w, F2* d) {
+    uint32_t n[16];
+#pragma unroll
+    for (int q = 0; q < 4; q++) {              // 4 pixels = 3 words
+        const uint32_t* x = w + 3 * q;
+        n[4 * q] = luma_num<0>(x[0], x[0]); n[4 * q + 1] = luma_num<3>(x[0], x[1]);
+        n[4 * q + 2] = luma_num<2>(x[1], x[2]); n[4 * q + 3] = luma_num<1>(x[2], x[2]);
+    }
+    uint32_t f[16], least = 0xffffffffu;
+#pragma unroll
+    for (int p = 0; p < 16; p++) f[p] = div1000_bits(n[p], least);
+    if (least < 2000000u) {                          // exact multiple of 1000 somewhere in the row: rare
+#pragma unroll
+        for (int p = 0; p < 16; p++) {
+            if (n[p] * 4294968u < 2000000u) {
+                int b = byte_of(w[(3 * p) >> 2], (3 * p) & 3);
+                int g = byte_of(w[(3 * p + 1) >> 2], (3 * p + 1) & 3);
+                int r = byte_of(w[(3 * p + 2) >> 2], (3 * p + 2) & 3);
+                f[p] = 0x4B000000u | (uint32_t) luma_exact_call(r, g, b);
+            }
+        }
+    }
+#pragma unroll
+    for (int x = 0; x < 8; x++) d[x] = centre_pair(f[x], f[8 + x]);
+}
+
+// 16 pixels (48 bytes) in 12 words -> (Cb, Cr) pairs of the 8 even pixels (color.c:82-83)
+__device__ __forceinline__ void chroma_row_pair(const uint32_t* w, F2* d) {
+    constexpr int BG_CB = (5000 & 0xffff) | (-3313 * 65536), R_CB = -1687 & 0xffff;
+    constexpr int BG_CR = (-813 & 0xffff) | (-4187 * 65536), R_CR = 5000;
+    uint32_t nb[8], nr[8];
+#pragma unroll
+    for (int x = 0; x < 8; x += 2) {
+        const int wa = (6 * x) >> 2;               // pixels 0,4,8,12 start at byte 0 of words 0,3,6,9
+        nb[x] = (uint32_t) dp2a_hi_s(R_CB, w[wa], dp2a_lo_s(BG_CB, w[wa], 1280000));
+        nr[x] = (uint32_t) dp2a_hi_s(R_CR, w[wa], dp2a_lo_s(BG_CR, w[wa], 1280000));
+        const int wb = (6 * (x + 1)) >> 2;         // pixels 2,6,10,14 start at byte 2 of words 1,4,7,10
+        nb[x + 1] = (uint32_t) dp2a_lo_s(R_CB, w[wb + 1], dp2a_hi_s(BG_CB, w[wb], 1280000));
+        nr[x + 1] = (uint32_t) dp2a_lo_s(R_CR, w[wb + 1], dp2a_hi_s(BG_CR, w[wb], 1280000));
+    }
+    uint32_t fb[8], fr[8], least = 0xffffffffu;
+#pragma unroll
+    for (int x = 0; x < 8; x++) { fb[x] = div10000_bits(nb[x], least); fr[x] = div10000_bits(nr[x], least); }
+    if (least < 417800u) {
+#pragma unroll
+        for (int x = 0; x < 8; x++) {
+            const bool mb_ = nb[x] - (__umulhi(nb[x], 3435974u) >> 3) * 10000u == 0u;
+            const bool mr_ = nr[x] - (__umulhi(nr[x], 3435974u) >> 3) * 10000u == 0u;
+            if (mb_ || mr_) {
+                int b = byte_of(w[(6 * x) >> 2], (6 * x) & 3);
+                int g = byte_of(w[(6 * x + 1) >> 2], (6 * x + 1) & 3);
+                int r = byte_of(w[(6 * x + 2) >> 2], (6 * x + 2) & 3);
+                if (mb_) fb[x] = 0x4B000000u | (uint32_t) chroma_exact_call(r, g, b, 0);
+                if (mr_) fr[x] = 0x4B000000u | (uint32_t) chroma_exact_call(r, g, b, 1);
+            }
+        }
+    }
+#pragma unroll
+    for (int x = 0; x < 8; x++) d[x] = centre_pair(fb[x], fr[x]);
+}
+
 // 8 pixels (24 bytes B,G,R,...) in 6 words -> 8 centred luma samples
 __device__ __forceinline__ void luma_row(const uint32_t* w, float* d) {
     uint32_t n[8];
@@ -292,6 +379,23 @@ extern "C" int awi_debug_phase_clocks(unsigned long long* out, int reset) {
 #define PHASE_INIT() do { } while (0)
 #endif
 
+// Phase B deals a tile's TILE_MB/2 luma iterations round-robin to the warps; the TILE_MB/4 chroma iterations are
+// handed out so that every warp ends up with the same total where that is possible (32 macroblocks, 6 warps:
+// warps 0-3 do 3 luma + 1 chroma, warps 4-5 do 2 luma + 2 chroma).  chroma_first(w) = first chroma iteration of warp w.
+__host__ __device__ constexpr int chroma_first(int w) {
+    constexpr int LUMA_IT = TILE_MB / 2, CHROMA_IT = TILE_MB / 4, TOTAL = LUMA_IT + CHROMA_IT;
+    int at = 0;
+    for (int i = 0; i < w; i++) {
+        const int luma = LUMA_IT / NWARPS + (i < LUMA_IT % NWARPS ? 1 : 0);
+        int share = (TOTAL + NWARPS - 1) / NWARPS - luma;          // bring warp i up to the even share
+        if (share < 0) share = 0;
+        if (at + share > CHROMA_IT) share = CHROMA_IT - at;
+        at += share;
+    }
+    return w >= NWARPS ? CHROMA_IT : at;
+}
+static_assert(chroma_first(NWARPS) == TILE_MB / 4, "every chroma iteration is handed to some warp");
+
 // ---------------------------------------------------------------- the kernel
 __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncParams P) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -379,9 +483,12 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
     __syncthreads();
     PHASE_MARK(1);
 
-    // ---- B: colour + DCT + quantise; 8 lanes per block, 4 blocks per warp per iteration.
-    //      48 iterations per tile (32 of luma blocks, 16 of Cb/Cr pairs) are dealt round-robin to the six
-    //      warps, so every warp gets the same mix and they reach the barrier together.
+    // ---- B: colour + DCT + quantise.  8 lanes per PAIR of 8x8 blocks, 4 pairs (8 blocks) per warp per iteration:
+    //      a lane carries row v (then column v) of two blocks in packed f32x2 registers, so every butterfly and
+    //      quantiser operation is one FADD2 / FMUL2 / FFMA2 for both.  Pairs share their pixels: the left and right
+    //      luma block of a macroblock half (one 48-byte row piece), or the Cb and Cr block of a macroblock (the same
+    //      even pixels) — and their chunks are neighbours (types 0/1, 2/3, 4/5), 64 bytes apart.
+    //      A tile is 16 luma iterations (2 macroblocks each) + 8 chroma iterations (4 macroblocks each), four per warp.
     {
         const int v = lane & 7, jb = lane >> 3;                   // v: my row in pass 1, my column in pass 2
         // per-lane quantiser constants for natural positions (u, v), u = 0..7, and where
@@ -390,92 +497,109 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
         int pos[8];                                               // scan positions of my 8 coefficients
 #pragma unroll
         for (int u = 0; u < 8; u++) pos[u] = unscan_rt(8 * u + v);
-        float* tr = S.tr[warp];                                   // 4 blocks x 72 floats: 8 rows of 8, block stride 8 mod 32
-        float4* const tr_row = reinterpret_cast<float4*>(tr + jb * 72 + v * 8);
-        const int tr_sw = v >> 2;
-        const float* const tr_col0 = tr + jb * 72 + v;
-        const float* const tr_col1 = tr + jb * 72 + (v ^ 4);
+        uint8_t* const trg = S.tr[warp] + jb * TR_GROUP + (jb >> 1) * 64 + (jb & 1) * 64;
+        uint4* const tr_row = reinterpret_cast<uint4*>(trg + v * TR_ROW);                        // my row goes out as 4 x 128 bits
+        const unsigned long long* const tr_col = reinterpret_cast<const unsigned long long*>(trg + v * 8);   // my column comes back
         uint8_t* coefb = reinterpret_cast<uint8_t*>(S.coef);
-        const int cBG = jb & 1 ? pack16(-813, -4187) : pack16(5000, -3313), cR = jb & 1 ? pack16(5000, 0) : pack16(-1687, 0);
 
         auto iteration = [&](auto kind, int j) {
             constexpr bool chroma = decltype(kind)::value;
             // one ambiguity threshold for every position (the tightest of the table): a few more exact
             // recomputations, but the per-coefficient test is a running maximum and 8 registers are saved
             constexpr float gt = chroma ? AWI_GT_MIN_CHROMA : AWI_GT_MIN_LUMA;
-            int mb, type;
-            if (!chroma) {            // j = 16*half + 8*block-row + it; 32 horizontally adjacent blocks per (half, block-row)
-                const int c = ((j >> 4) << 5) + 4 * (j & 7) + jb;
-                mb = c >> 1;
-                type = (((j >> 3) & 1) << 1) | (c & 1);
-            } else {                  // (Cb, Cr) pairs of two macroblocks
+            int mb, type;                                         // type of the pair's first block; the second is type + 1
+            F2 d[8];
+            if (!chroma) {            // macroblock 2j or 2j+1, upper (Y00, Y01) or lower (Y10, Y11) half
                 mb = 2 * j + (jb >> 1);
-                type = 4 + (jb & 1);
+                type = (jb & 1) << 1;
+                const uint4* s4 = reinterpret_cast<const uint4*>(S.raw + (((jb & 1) << 3) + v) * PITCH + mb * 48);
+                const uint4 a = s4[0], b = s4[1], c4 = s4[2];
+                const uint32_t w[12] = { a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w, c4.x, c4.y, c4.z, c4.w };
+                luma_row_pair(w, d);
+            } else {                  // (Cb, Cr) of macroblock 4j + jb
+                mb = 4 * j + jb;
+                type = 4;
+                const uint4* s4 = reinterpret_cast<const uint4*>(S.raw + 2 * v * PITCH + mb * 48);
+                const uint4 a = s4[0], b = s4[1], c4 = s4[2];
+                const uint32_t w[12] = { a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w, c4.x, c4.y, c4.z, c4.w };
+                chroma_row_pair(w, d);
             }
             const int chunk = mb * 6 + type;
             const bool active = mb < n_mb;
-            float d[8];
-            if (!chroma) {
-                const uint8_t* src = S.raw + (((type >> 1) << 3) + v) * PITCH + mb * 48 + (type & 1) * 24;
-                const uint2* s2 = reinterpret_cast<const uint2*>(src);
-                uint2 a = s2[0], b = s2[1], c2 = s2[2];
-                uint32_t w[6] = { a.x, a.y, b.x, b.y, c2.x, c2.y };
-                luma_row(w, d);
-            } else {
-                const uint4* s4 = reinterpret_cast<const uint4*>(S.raw + 2 * v * PITCH + mb * 48);
-                uint4 a = s4[0], b = s4[1], c4 = s4[2];
-                uint32_t w[12] = { a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w, c4.x, c4.y, c4.z, c4.w };
-                chroma_row(w, d, cBG, cR, jb & 1);
+            aan8_t<F2>(d[0], d[1], d[2], d[3], d[4], d[5], d[6], d[7]);           // row pass
+            // transpose through shared memory: a row of pairs goes out as four 128-bit stores, a column comes
+            // back as eight 64-bit loads (both conflict-free, see TR_ROW)
+            __syncwarp();
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                float x0, x1, y0, y1;
+                f2_unpack(d[2 * k], x0, x1);
+                f2_unpack(d[2 * k + 1], y0, y1);
+                tr_row[k] = make_uint4(__float_as_uint(x0), __float_as_uint(x1), __float_as_uint(y0), __float_as_uint(y1));
             }
-            aan8(d[0], d[1], d[2], d[3], d[4], d[5], d[6], d[7]);                 // row pass
-            // transpose through shared memory: a row goes out as two 128-bit stores (the halves swap places in
-            // rows 4-7, so the eight rows of a block cover all 32 banks), a column comes back as 8 scalar loads
-            __syncwarp();
-            tr_row[tr_sw] = make_float4(d[0], d[1], d[2], d[3]);
-            tr_row[tr_sw ^ 1] = make_float4(d[4], d[5], d[6], d[7]);
             __syncwarp();
 #pragma unroll
-            for (int u = 0; u < 4; u++) d[u] = tr_col0[8 * u];
-#pragma unroll
-            for (int u = 4; u < 8; u++) d[u] = tr_col1[8 * u];
-            aan8(d[0], d[1], d[2], d[3], d[4], d[5], d[6], d[7]);                 // column pass: d[u] = coefficient (u, v)
+            for (int u = 0; u < 8; u++) d[u].v = tr_col[u * (TR_ROW / 8)];
+            aan8_t<F2>(d[0], d[1], d[2], d[3], d[4], d[5], d[6], d[7]);           // column pass: d[u] = coefficients (u, v) of both blocks
 
-            float t[8];
-            const float dist0 = quant_absdiff(d[0], gk[0], gc[0], t[0]);
-            float dist = v == 0 ? 0.0f : dist0;              // the DC (u = v = 0) is exact, never ambiguous
+            F2 t[8];
+            float dist = 0.0f;
 #pragma unroll
-            for (int u = 1; u < 8; u++) dist = fmaxf(dist, quant_absdiff(d[u], gk[u], gc[u], t[u]));
+            for (int u = 0; u < 8; u++) {
+                const F2 df = quant_pair(d[u], gk[u], gc[u], t[u]);
+                float e0, e1;
+                f2_unpack(df, e0, e1);
+                if (u == 0) dist = v == 0 ? 0.0f : fmaxf(fabsf(e0), fabsf(e1));      // the DC (u = v = 0) is exact, never ambiguous
+                else dist = fmaxf(dist, fmaxf(fabsf(e0), fabsf(e1)));
+            }
             if (active) {
                 uint8_t* cb = coefb + chunk * 64;
                 // lane v = 0 holds the DC position: d[0] there is the exact integer sum of the 64 centred
                 // samples (|S| <= 8192).  It is left as a sum; phase D turns sums into quantised DCs once per
                 // chunk (dct.c:50 + :123 in integers).  The magic add reads the integer without a conversion.
-                if (v == 0) S.dc[(mb + 1) * 6 + type] = __float_as_int(d[0] + 12582912.0f) - 0x4B400000;
-                else cb[pos[0]] = (uint8_t) __float_as_uint(t[0]);
 #pragma unroll
-                for (int u = 1; u < 8; u++) cb[pos[u]] = (uint8_t) __float_as_uint(t[u]);
+                for (int u = 0; u < 8; u++) {
+                    float t0, t1;
+                    f2_unpack(t[u], t0, t1);
+                    if (u == 0 && v == 0) {
+                        float s0, s1;
+                        f2_unpack(d[0], s0, s1);
+                        int* dcp = &S.dc[(mb + 1) * 6 + type];
+                        dcp[0] = __float_as_int(s0 + 12582912.0f) - 0x4B400000;
+                        dcp[1] = __float_as_int(s1 + 12582912.0f) - 0x4B400000;
+                    } else {
+                        uint8_t* q = cb + pos[u];
+                        q[0] = (uint8_t) __float_as_uint(t0);
+                        q[64] = (uint8_t) __float_as_uint(t1);
+                    }
+                }
             }
             const bool mine = active && dist > gt;
-            const unsigned any = __ballot_sync(0xffffffffu, mine);
-            if (any) {                // rare: remember which coefficients to redo exactly
+            if (__any_sync(0xffffffffu, mine)) {                // rare: remember which coefficients to redo exactly
                 if (mine) {
-                    unsigned long long m = 0;
-                    float tmp;
+                    unsigned long long m0 = 0, m1 = 0;
 #pragma unroll
-                    for (int u = 0; u < 8; u++)
-                        if ((u > 0 || v > 0) && quant_absdiff(d[u], gk[u], gc[u], tmp) > gt) m |= 1ull << (8 * u + v);
-                    atomicOr(&S.amb[chunk], m);
+                    for (int u = 0; u < 8; u++) {
+                        if (u > 0 || v > 0) {
+                            float x0, x1, tmp;
+                            f2_unpack(d[u], x0, x1);
+                            if (quant_absdiff(x0, gk[u], gc[u], tmp) > gt) m0 |= 1ull << (8 * u + v);
+                            if (quant_absdiff(x1, gk[u], gc[u], tmp) > gt) m1 |= 1ull << (8 * u + v);
+                        }
+                    }
+                    // the lane that turns a chunk's mask from zero to non-zero lists the chunk (once)
+                    if (m0 && atomicOr(&S.amb[chunk], m0) == 0ull) S.amb_list[atomicAdd(&S.amb_count, 1)] = (uint16_t) chunk;
+                    if (m1 && atomicOr(&S.amb[chunk + 1], m1) == 0ull) S.amb_list[atomicAdd(&S.amb_count, 1)] = (uint16_t) (chunk + 1);
                 }
-                const unsigned grp = (any >> (8 * jb)) & 0xffu;
-                if (grp && v == __ffs((int) grp) - 1) S.amb_list[atomicAdd(&S.amb_count, 1)] = (uint16_t) chunk;
             }
         };
 #pragma unroll
         for (int u = 0; u < 8; u++) { gk[u] = d_gk[0][8 * u + v]; gc[u] = d_gc[0][8 * u + v]; }
-        for (int j = warp; j < TILE_MB; j += NWARPS) iteration(std::false_type{}, j);
+        for (int j = warp; j < TILE_MB / 2; j += NWARPS) iteration(std::false_type{}, j);
 #pragma unroll
         for (int u = 0; u < 8; u++) { gk[u] = d_gk[1][8 * u + v]; gc[u] = d_gc[1][8 * u + v]; }
-        for (int j = (warp + NWARPS - TILE_MB % NWARPS) % NWARPS; j < TILE_MB / 2; j += NWARPS) iteration(std::true_type{}, j);
+        // the warps that got one luma iteration less take one chroma iteration more
+        for (int j = chroma_first(warp); j < chroma_first(warp + 1); j++) iteration(std::true_type{}, j);
     }
 
     PHASE_MARK(2);

@@ -208,24 +208,54 @@ AWI_HD float centred(int s) { return u2f(0x4B000000u | (uint32_t) s) - 8388736.0
 // 8-point AAN butterfly (5 multiplies, 29 adds), outputs scaled by a_k (a_0 = 1,
 // a_k = sqrt2*cos(k*pi/16)) relative to the orthonormal-free sum  sum_x d[x] cos((2x+1)k pi/16).
 // With integer inputs |d| <= 2^21 output 0 (the plain sum) and 4 are exact.
-AWI_HD void aan8(float& d0, float& d1, float& d2, float& d3, float& d4, float& d5, float& d6, float& d7) {
-    float t0 = d0 + d7, t7 = d0 - d7, t1 = d1 + d6, t6 = d1 - d6;
-    float t2 = d2 + d5, t5 = d2 - d5, t3 = d3 + d4, t4 = d3 - d4;
-    float t10 = t0 + t3, t13 = t0 - t3, t11 = t1 + t2, t12 = t1 - t2;
-    d0 = t10 + t11;
-    d4 = t10 - t11;
-    float z1 = (t12 + t13) * 0.707106781f;
-    d2 = t13 + z1;
-    d6 = t13 - z1;
-    t10 = t4 + t5; t11 = t5 + t6; t12 = t6 + t7;
-    float z5 = (t10 - t12) * 0.382683433f;
-    float z2 = fma_rn(0.541196100f, t10, z5);
-    float z4 = fma_rn(1.306562965f, t12, z5);
-    float z3 = t11 * 0.707106781f;
-    float z11 = t7 + z3, z13 = t7 - z3;
-    d5 = z13 + z2; d3 = z13 - z2;
-    d1 = z11 + z4; d7 = z11 - z4;
+// The butterfly is written once over an arithmetic type T: float (one block per lane; also what tests/emul
+// compiles for the host) or F2 (two blocks per lane in packed f32x2 registers, sm_100a).  Every operation is an
+// IEEE fp32 add/sub/mul/fma with round-to-nearest on each element, so both instantiations give the same bits.
+AWI_HD float op_add(float a, float b) { return a + b; }
+AWI_HD float op_sub(float a, float b) { return a - b; }
+AWI_HD float op_mulc(float a, float c) { return a * c; }
+AWI_HD float op_fmac(float c, float a, float b) { return fma_rn(c, a, b); }       // c*a + b, one rounding
+
+template <class T>
+AWI_HD void aan8_t(T& d0, T& d1, T& d2, T& d3, T& d4, T& d5, T& d6, T& d7) {
+    T t0 = op_add(d0, d7), t7 = op_sub(d0, d7), t1 = op_add(d1, d6), t6 = op_sub(d1, d6);
+    T t2 = op_add(d2, d5), t5 = op_sub(d2, d5), t3 = op_add(d3, d4), t4 = op_sub(d3, d4);
+    T t10 = op_add(t0, t3), t13 = op_sub(t0, t3), t11 = op_add(t1, t2), t12 = op_sub(t1, t2);
+    d0 = op_add(t10, t11);
+    d4 = op_sub(t10, t11);
+    T z1 = op_mulc(op_add(t12, t13), 0.707106781f);
+    d2 = op_add(t13, z1);
+    d6 = op_sub(t13, z1);
+    t10 = op_add(t4, t5); t11 = op_add(t5, t6); t12 = op_add(t6, t7);
+    T z5 = op_mulc(op_sub(t10, t12), 0.382683433f);
+    T z2 = op_fmac(0.541196100f, t10, z5);
+    T z4 = op_fmac(1.306562965f, t12, z5);
+    T z3 = op_mulc(t11, 0.707106781f);
+    T z11 = op_add(t7, z3), z13 = op_sub(t7, z3);
+    d5 = op_add(z13, z2); d3 = op_sub(z13, z2);
+    d1 = op_add(z11, z4); d7 = op_sub(z11, z4);
 }
+AWI_HD void aan8(float& d0, float& d1, float& d2, float& d3, float& d4, float& d5, float& d6, float& d7) {
+    aan8_t<float>(d0, d1, d2, d3, d4, d5, d6, d7);
+}
+
+#if defined(__CUDACC__)
+// Two fp32 values in one 64-bit register pair, operated on by the packed instructions of sm_100
+// (add/sub/mul/fma.rn.f32x2 -> FADD2 / FMUL2 / FFMA2): one issue slot for two blocks' worth of arithmetic.
+// Written as explicit PTX, so --fmad=false has nothing to contract and each element is rounded exactly like
+// the scalar instruction would round it.
+struct F2 { unsigned long long v; };
+AWI_D F2 f2_pack(float lo, float hi) { F2 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r.v) : "f"(lo), "f"(hi)); return r; }
+AWI_D void f2_unpack(F2 a, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(a.v)); }
+AWI_D F2 f2_splat(float c) { return f2_pack(c, c); }
+AWI_D F2 op_add(F2 a, F2 b) { F2 r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r.v) : "l"(a.v), "l"(b.v)); return r; }
+AWI_D F2 op_sub(F2 a, F2 b) { F2 r; asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r.v) : "l"(a.v), "l"(b.v)); return r; }
+AWI_D F2 op_mulc(F2 a, float c) { F2 r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r.v) : "l"(a.v), "l"(f2_splat(c).v)); return r; }
+AWI_D F2 op_fmac(float c, F2 a, F2 b) {
+    F2 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r.v) : "l"(f2_splat(c).v), "l"(a.v), "l"(b.v)); return r;
+}
+AWI_D F2 f2_fma(F2 a, F2 b, F2 c) { F2 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r.v) : "l"(a.v), "l"(b.v), "l"(c.v)); return r; }
+#endif
 
 // Quantised DC from the exact sample sum S = sum(p - 128)  (dct.c:50 at u=v=0: the fp64
 // scale 0.25*cu*cv is 0x3FBFFFFFFFFFFFFE, a hair under 1/8, so (int)(scale*S) is
@@ -256,6 +286,19 @@ AWI_HD float quant_absdiff(float x, float gk, float gc, float& t) {      // |g -
     return diff < 0 ? -diff : diff;
 }
 AWI_HD bool quant_flag(float x, float gk, float gc, float gt, float& t) { return quant_absdiff(x, gk, gc, t) > gt; }
+#if defined(__CUDACC__)
+// The same for the two blocks of a pair (same position, same constants): 2 LOP3 + FFMA2 + 3 FADD2; the caller
+// folds |diff| of both halves into its running maximum with one 3-input FMNMX.
+AWI_D F2 quant_pair(F2 x, float gk, float gc, F2& t) {
+    float x0, x1;
+    f2_unpack(x, x0, x1);
+    const float s0 = u2f(f2u(gc) | (~f2u(x0) & 0x80000000u)), s1 = u2f(f2u(gc) | (~f2u(x1) & 0x80000000u));   // -sign(x)*gc
+    const F2 g = f2_fma(x, f2_splat(gk), f2_pack(s0, s1));
+    const F2 M = f2_splat(12582912.0f);
+    t = op_add(g, M);
+    return op_sub(g, op_sub(t, M));                 // g - rn(g), exact
+}
+#endif
 
 // Fast DCT + quantise + scan-order pack of one 8x8 block held in registers.
 //   d[64]  in: centred samples, natural [y][x] order (destroyed)
