@@ -9,11 +9,13 @@
 //   A  the tile's 16 pixel rows (bottom-up BGR) -> smem: 16 bulk asynchronous copies (TMA,
 //      mbarrier completion) for full interior tiles, coalesced 128-bit loads with edge
 //      handling otherwise
-//   B  8 lanes per 8x8 block (one image row each, then one column each): colour ->
-//      AAN row pass in registers -> 8x8 transpose through smem -> AAN column
-//      pass -> quantise (+ambiguity flags) with per-lane constants held in registers
-//      -> scan-order int8 coefficients in smem;  exact DC;  halo macroblock DCs.
-//      The tile's 48 iterations (4 blocks each) are dealt round-robin to the warps.
+//   B1 colour: one thread per 16-pixel row piece of a macroblock -> Y (and, on even rows, Cb/Cr of the even
+//      pixels) as bytes in smem, laid out as "pair rows": 8 samples of one block next to 8 of its partner
+//   B2 8 lanes per PAIR of 8x8 blocks (one row each, then one column each), both blocks of a pair in packed
+//      f32x2 registers (FADD2/FMUL2/FFMA2): AAN row pass -> 8x8 transpose through smem -> AAN column pass ->
+//      quantise (+ambiguity flags) with per-lane constants -> scan-order int8 coefficients in smem;
+//      exact DC;  halo macroblock DCs.  One loop body serves luma and chroma pairs; the tile's 24
+//      iterations (8 blocks each) are dealt round-robin to the warps.
 //   C  flagged coefficients recomputed warp-cooperatively in the reference's exact
 //      operation order
 //   D  one thread per chunk: run-length symbols + bit packing into a smem slot
@@ -46,31 +48,35 @@ constexpr int PITCH = TILE_MB * 48 + 16;         // smem bytes per pixel row: 38
                                                  // block land 4 banks apart, conflict-free 64-bit row reads
 constexpr int RAW_BYTES = 16 * PITCH;            // 24832
 constexpr int SLOT = 124;                        // staging bytes per chunk (max 121), 31 words: conflict-free
-constexpr int COMPACT_CAP = THREADS * 64;        // compacted tile lives in the (dead) coefficient buffer
-constexpr int TR_ROW = 80;                        // phase B transposes, per lane group: 8 rows of 8 (block A, block B) float pairs = 64 B,
+constexpr int COEF_BYTES = THREADS * 64;         // int8[64] per chunk
+constexpr int SAMP_MB = 400;                     // sample bytes per macroblock: 16 luma pair rows + 8 chroma pair rows of 16 B, + 16 B so
+                                                 // that macroblocks sit 4 banks apart (eight of them are written side by side)
+constexpr int SAMP_BYTES = TILE_MB * SAMP_MB;    // 12800
+constexpr int COMPACT_CAP = (RAW_BYTES - 16) & ~15;   // the compacted tile lives in the (dead) pixel/coefficient buffer: always fits
+constexpr int TR_ROW = 80;                        // phase B2 transposes, per lane group: 8 rows of 8 (block A, block B) float pairs = 64 B,
 constexpr int TR_GROUP = 8 * TR_ROW;              // rows 80 B apart (20 banks: the eight 128-bit row stores of a group cover all 32 banks),
 constexpr int TR_BYTES = 4 * TR_GROUP + 2 * 64;   // groups 640 B apart, 64 B more in front of groups 1, 2 (carried on) and 3 (the two groups of a half-warp
                                                   // read 64-byte rows 16 banks apart)
-static_assert(THREADS * SLOT <= RAW_BYTES, "chunk slots alias the raw tile");
 static_assert(THREADS == 2 * TILE_MB * 3, "loader: one fixed (macroblock, 16-byte piece) per thread, two rows per pass");
 static_assert(THREADS == TILE_MB * 6, "one thread per chunk in phases D-F");
+static_assert(TILE_MB % 8 == 0 && (TILE_MB * 24) % THREADS == 0, "phase B1: 24 row pieces per macroblock, whole passes");
 
 struct __align__(16) EncSmem {
-    uint8_t raw[RAW_BYTES];                      // phase A-C: pixels; phase D-F: chunk slots
+    uint8_t raw[RAW_BYTES];                      // phase A-B1: pixels; B2-D: coefficients (int8[64] per chunk, scan order); E-F: compacted tile
+    uint8_t work[SAMP_BYTES + NWARPS * TR_BYTES];   // B1-C: samples [0, SAMP_BYTES), B2: transposes behind them; D-F: chunk slots
     uint8_t halo[16 * 48];                       // macroblock preceding the tile
-    uint32_t coef[THREADS * 16];                 // int8[64] per chunk, scan order; phase E-F: compacted tile
-    uint8_t tr[NWARPS][TR_BYTES];                // phase B transposes
     unsigned long long amb[THREADS];             // per chunk: natural positions to recompute
-    int dc[(TILE_MB + 1) * 6];                   // quantised DCs, [0] = halo macroblock
+    short dc[(TILE_MB + 1) * 6];                 // block sample sums (the DCs before quantisation), [0] = halo macroblock
     int halo_sum[6];
     uint32_t warp_tot[NWARPS];
-    uint16_t amb_list[THREADS];                  // chunks with flagged coefficients
+    uint8_t amb_list[THREADS];                   // chunks with flagged coefficients
     int amb_count;
     unsigned long long tile_base;
     unsigned long long load_bar;                 // mbarrier the bulk copies of phase A complete on
     int tile;
 };
-
+static_assert(THREADS * SLOT <= SAMP_BYTES + NWARPS * TR_BYTES, "chunk slots alias the sample and transpose buffers");
+static_assert(COEF_BYTES <= RAW_BYTES && THREADS <= 256, "coefficients alias the pixel buffer; chunk numbers fit a byte");
 static_assert(sizeof(EncSmem) + 1024 <= (228 * 1024) / ENC_MIN_CTAS, "ENC_MIN_CTAS tiles (+1 KB each the system keeps) must fit an SM's 228 KB");
 
 // chunk index inside the tile: 6*macroblock + type, type 0..3 = Y[i][j], 4 = Cb, 5 = Cr
@@ -177,45 +183,28 @@ __device__ __forceinline__ uint32_t luma_num(uint32_t wa, uint32_t wb) {
     return dp2a_lo_u(GR, wb, dp2a_hi_u(ZB, wa, 0u));
 }
 
-// n / 1000 and "n is an exact multiple of 1000" from one 32x32->64 multiply:
-// n * 4294968 = 2^32 * (n/1000) + 0.704 n, so the low word is below 179521 exactly for multiples
-// and above 4294967 otherwise (n <= 255000).
-__device__ __forceinline__ uint32_t div1000(uint32_t n, bool& multiple) {
-    unsigned long long p = (unsigned long long) n * 4294968ull;
-    multiple = (uint32_t) p < 2000000u;
-    return (uint32_t) (p >> 32);
-}
-// n / 10000 likewise: n * 3435974 = 2^35 * (n/10000) + 0.1632 n (n <= 2560000); bits 3..34 of the
-// product are below 52225 exactly for multiples and above 429495 otherwise.
-__device__ __forceinline__ uint32_t div10000(uint32_t n, bool& multiple) {
-    unsigned long long p = (unsigned long long) n * 3435974ull;
-    uint32_t hi = (uint32_t) (p >> 32), lo = (uint32_t) p;
-    multiple = __funnelshift_l(lo, hi, 29) < 200000u;
-    return hi >> 3;
-}
-
-// Quotient as the bit pattern of the float 2^23 + q (0x4B000000 | q): two of them side by side are a packed pair,
-// and one packed subtraction of 2^23 + 128 turns both into centred samples (float)(q - 128).
-__device__ __forceinline__ uint32_t div1000_bits(uint32_t n, uint32_t& least_low) {
-    const unsigned long long p = (unsigned long long) n * 4294968ull;
-    least_low = min(least_low, (uint32_t) p);                   // an exact multiple of 1000 shows as a low word below 2000000
-    return (uint32_t) (p >> 32) | 0x4B000000u;
-}
-// n / 10000: the quotient sits in bits 35..; the cheap test looks at the low word only (a multiple has bits
+// n / 1000 and n / 10000 for phase B1, with the exact-multiple test folded into a running minimum of the low
+// product words (one 3-input minimum per two samples): an exact multiple of 1000 shows as a low word below
+// 2000000; for 10000 the quotient sits in bits 35.. and only the low word is looked at (a multiple has bits
 // 0..34 below 417800, so its low word is below that too; the few non-multiples that pass are told apart by
 // the exact remainder test on the slow path).
-__device__ __forceinline__ uint32_t div10000_bits(uint32_t n, uint32_t& least_low) {
+__device__ __forceinline__ uint32_t div1000_q(uint32_t n, uint32_t& least_low) {
+    const unsigned long long p = (unsigned long long) n * 4294968ull;
+    least_low = min(least_low, (uint32_t) p);
+    return (uint32_t) (p >> 32);
+}
+__device__ __forceinline__ uint32_t div10000_q(uint32_t n, uint32_t& least_low) {
     const unsigned long long p = (unsigned long long) n * 3435974ull;
     least_low = min(least_low, (uint32_t) p);
-    return ((uint32_t) (p >> 32) >> 3) | 0x4B000000u;
+    return (uint32_t) (p >> 32) >> 3;
 }
-__device__ __forceinline__ F2 centre_pair(uint32_t a, uint32_t b) {
-    return op_sub(f2_pack(__uint_as_float(a), __uint_as_float(b)), f2_splat(8388736.0f));
+__device__ __forceinline__ uint32_t pack4(uint32_t a, uint32_t b, uint32_t c, uint32_t d) {      // four values 0..255 -> bytes, a lowest
+    return __byte_perm(__byte_perm(a, b, 0x0040), __byte_perm(c, d, 0x0040), 0x5410);
 }
 
-// 16 pixels (48 bytes) in 12 words -> the 16 centred luma samples of one image row of a macroblock, as
-// eight (left block, right block) pairs
-__device__ __forceinline__ void luma_row_pair(const uint32_t* w, F2* d) {
+// 16 pixels (48 bytes B,G,R,...) in 12 words -> their 16 luma samples (color.c:31 + utils.c:10-17) as bytes:
+// .x/.y = the row of the left 8x8 block, .z/.w = of the right one
+__device__ __forceinline__ uint4 luma_piece(const uint32_t* w) {
     uint32_t n[16];
 #pragma unroll
     for (int q = 0; q < 4; q++) {              // 4 pixels = 3 words
@@ -225,24 +214,24 @@ __device__ __forceinline__ void luma_row_pair(const uint32_t* w, F2* d) {
     }
     uint32_t f[16], least = 0xffffffffu;
 #pragma unroll
-    for (int p = 0; p < 16; p++) f[p] = div1000_bits(n[p], least);
-    if (least < 2000000u) {                          // exact multiple of 1000 somewhere in the row: rare
+    for (int p = 0; p < 16; p++) f[p] = div1000_q(n[p], least);
+    if (least < 2000000u) {                          // an exact multiple of 1000 somewhere in the piece (grey pixels are)
 #pragma unroll
         for (int p = 0; p < 16; p++) {
             if (n[p] * 4294968u < 2000000u) {
                 int b = byte_of(w[(3 * p) >> 2], (3 * p) & 3);
                 int g = byte_of(w[(3 * p + 1) >> 2], (3 * p + 1) & 3);
                 int r = byte_of(w[(3 * p + 2) >> 2], (3 * p + 2) & 3);
-                f[p] = 0x4B000000u | (uint32_t) luma_exact_call(r, g, b);
+                f[p] = (uint32_t) luma_exact_call(r, g, b);
             }
         }
     }
-#pragma unroll
-    for (int x = 0; x < 8; x++) d[x] = centre_pair(f[x], f[8 + x]);
+    return make_uint4(pack4(f[0], f[1], f[2], f[3]), pack4(f[4], f[5], f[6], f[7]),
+                      pack4(f[8], f[9], f[10], f[11]), pack4(f[12], f[13], f[14], f[15]));
 }
 
-// 16 pixels (48 bytes) in 12 words -> (Cb, Cr) pairs of the 8 even pixels (color.c:82-83)
-__device__ __forceinline__ void chroma_row_pair(const uint32_t* w, F2* d) {
+// 16 pixels (48 bytes) in 12 words -> Cb (.x/.y) and Cr (.z/.w) of the 8 even pixels (color.c:32-33,82-83) as bytes
+__device__ __forceinline__ uint4 chroma_piece(const uint32_t* w) {
     constexpr int BG_CB = (5000 & 0xffff) | (-3313 * 65536), R_CB = -1687 & 0xffff;
     constexpr int BG_CR = (-813 & 0xffff) | (-4187 * 65536), R_CR = 5000;
     uint32_t nb[8], nr[8];
@@ -257,51 +246,25 @@ __device__ __forceinline__ void chroma_row_pair(const uint32_t* w, F2* d) {
     }
     uint32_t fb[8], fr[8], least = 0xffffffffu;
 #pragma unroll
-    for (int x = 0; x < 8; x++) { fb[x] = div10000_bits(nb[x], least); fr[x] = div10000_bits(nr[x], least); }
+    for (int x = 0; x < 8; x++) { fb[x] = div10000_q(nb[x], least); fr[x] = div10000_q(nr[x], least); }
     if (least < 417800u) {
 #pragma unroll
         for (int x = 0; x < 8; x++) {
-            const bool mb_ = nb[x] - (__umulhi(nb[x], 3435974u) >> 3) * 10000u == 0u;
-            const bool mr_ = nr[x] - (__umulhi(nr[x], 3435974u) >> 3) * 10000u == 0u;
+            const bool mb_ = nb[x] - fb[x] * 10000u == 0u, mr_ = nr[x] - fr[x] * 10000u == 0u;
             if (mb_ || mr_) {
                 int b = byte_of(w[(6 * x) >> 2], (6 * x) & 3);
                 int g = byte_of(w[(6 * x + 1) >> 2], (6 * x + 1) & 3);
                 int r = byte_of(w[(6 * x + 2) >> 2], (6 * x + 2) & 3);
-                if (mb_) fb[x] = 0x4B000000u | (uint32_t) chroma_exact_call(r, g, b, 0);
-                if (mr_) fr[x] = 0x4B000000u | (uint32_t) chroma_exact_call(r, g, b, 1);
+                if (mb_) fb[x] = (uint32_t) chroma_exact_call(r, g, b, 0);
+                if (mr_) fr[x] = (uint32_t) chroma_exact_call(r, g, b, 1);
             }
         }
     }
-#pragma unroll
-    for (int x = 0; x < 8; x++) d[x] = centre_pair(fb[x], fr[x]);
+    return make_uint4(pack4(fb[0], fb[1], fb[2], fb[3]), pack4(fb[4], fb[5], fb[6], fb[7]),
+                      pack4(fr[0], fr[1], fr[2], fr[3]), pack4(fr[4], fr[5], fr[6], fr[7]));
 }
 
-// 8 pixels (24 bytes B,G,R,...) in 6 words -> 8 centred luma samples
-__device__ __forceinline__ void luma_row(const uint32_t* w, float* d) {
-    uint32_t n[8];
-    n[0] = luma_num<0>(w[0], w[0]); n[1] = luma_num<3>(w[0], w[1]); n[2] = luma_num<2>(w[1], w[2]); n[3] = luma_num<1>(w[2], w[2]);
-    n[4] = luma_num<0>(w[3], w[3]); n[5] = luma_num<3>(w[3], w[4]); n[6] = luma_num<2>(w[4], w[5]); n[7] = luma_num<1>(w[5], w[5]);
-    bool any = false;
-#pragma unroll
-    for (int x = 0; x < 8; x++) {
-        bool mult;
-        d[x] = centred((int) div1000(n[x], mult));
-        any |= mult;
-    }
-    if (any) {                                       // exact multiple of 1000 somewhere in the row: rare
-#pragma unroll
-        for (int x = 0; x < 8; x++) {
-            if (n[x] * 4294968u < 2000000u) {          // same test as div1000
-                int b = byte_of(w[(3 * x) >> 2], (3 * x) & 3);
-                int g = byte_of(w[(3 * x + 1) >> 2], (3 * x + 1) & 3);
-                int r = byte_of(w[(3 * x + 2) >> 2], (3 * x + 2) & 3);
-                d[x] = centred(luma_exact_call(r, g, b));
-            }
-        }
-    }
-}
-
-// one colour-difference sample; cr selects the coefficient set
+// one colour-difference sample (halo macroblock sums); cr selects the coefficient set
 __device__ __forceinline__ int chroma_of(int r, int g, int b, bool cr) {
     int kr = cr ? 5000 : -1687, kg = cr ? -4187 : -3313, kb = cr ? -813 : 5000;
     uint32_t n = (uint32_t) (kr * r + kg * g + kb * b + 1280000);
@@ -310,51 +273,16 @@ __device__ __forceinline__ int chroma_of(int r, int g, int b, bool cr) {
     return (int) q;
 }
 
-// 16 pixels (48 bytes) in 12 words -> samples of the 8 even pixels (color.c:82-83).
-// cBG = kb | kg<<16, cR = kr: signed 16-bit coefficient pairs of the Cb or Cr row.
-__device__ __forceinline__ void chroma_row(const uint32_t* w, float* d, int cBG, int cR, int cr) {
-    uint32_t n[8];
-#pragma unroll
-    for (int x = 0; x < 8; x += 2) {
-        // even pixel 2x starts at byte 0 of w[3x/2*... ]: pixels 0,2,4,6 start at byte 0 of words 0,3,6,9;
-        // pixels 1,3,5,7 start at byte 2 of words 1,4,7,10
-        const int wa = (6 * x) >> 2;               // x even: 6x is a multiple of 4... (x = 0,2,4,6 -> words 0,3,6,9)
-        n[x] = (uint32_t) dp2a_hi_s(cR, w[wa], dp2a_lo_s(cBG, w[wa], 1280000));
-        const int wb = (6 * (x + 1)) >> 2;         // words 1,4,7,10, byte offset 2
-        n[x + 1] = (uint32_t) dp2a_lo_s(cR, w[wb + 1], dp2a_hi_s(cBG, w[wb], 1280000));
-    }
-    bool any = false;
-#pragma unroll
-    for (int x = 0; x < 8; x++) {
-        bool mult;
-        d[x] = centred((int) div10000(n[x], mult));
-        any |= mult;
-    }
-    if (any) {
-#pragma unroll
-        for (int x = 0; x < 8; x++) {
-            bool mult; (void) div10000(n[x], mult);
-            if (mult) {
-                int b = byte_of(w[(6 * x) >> 2], (6 * x) & 3);
-                int g = byte_of(w[(6 * x + 1) >> 2], (6 * x + 1) & 3);
-                int r = byte_of(w[(6 * x + 2) >> 2], (6 * x + 2) & 3);
-                d[x] = centred(chroma_exact_call(r, g, b, cr));
-            }
-        }
-    }
+// Sample bytes of a tile (phase B1 -> B2, C).  Macroblock m owns SAMP_MB bytes: 16 luma pair rows (row y: 8 samples of
+// the left block, 8 of the right one), then 8 chroma pair rows (row y: 8 Cb samples, 8 Cr samples).
+__device__ __forceinline__ int samp_row(int mb, int type, int y) {          // byte offset of row y of the pair that holds chunk type `type`
+    return mb * SAMP_MB + (type < 4 ? (((type >> 1) << 3) + y) * 16 : 256 + y * 16);
 }
-
-// sample (row y, column x) of chunk `chunk` of the tile, recomputed from the raw pixels
-__device__ __forceinline__ int sample_of(const EncSmem& S, int chunk, int y, int x) {
+__device__ __forceinline__ int sample_of(const uint8_t* samp, int chunk, int y, int x) {
     const int mb = chunk / 6, type = chunk - 6 * mb;
-    int row, col;
-    if (type < 4) { row = ((type >> 1) << 3) + y; col = mb * 48 + ((type & 1) * 8 + x) * 3; }
-    else { row = 2 * y; col = mb * 48 + 6 * x; }
-    const uint8_t* p = S.raw + row * PITCH + col;
-    int b = p[0], g = p[1], r = p[2];
-    if (type < 4) return luma_of(r, g, b);
-    return chroma_of(r, g, b, type == 5);
+    return samp[samp_row(mb, type, y) + ((type & 1) << 3) + x];
 }
+static_assert(AWI_GT_MIN_LUMA == AWI_GT_MIN_CHROMA, "phase B2 uses one ambiguity threshold for both tables");
 
 #ifdef ENC_PHASE_CLOCKS
 // debug build only (tools/phase_clocks.py): cycles per warp between phase marks, summed over all tiles.
@@ -378,23 +306,6 @@ extern "C" int awi_debug_phase_clocks(unsigned long long* out, int reset) {
 #define PHASE_MARK(i) do { } while (0)
 #define PHASE_INIT() do { } while (0)
 #endif
-
-// Phase B deals a tile's TILE_MB/2 luma iterations round-robin to the warps; the TILE_MB/4 chroma iterations are
-// handed out so that every warp ends up with the same total where that is possible (32 macroblocks, 6 warps:
-// warps 0-3 do 3 luma + 1 chroma, warps 4-5 do 2 luma + 2 chroma).  chroma_first(w) = first chroma iteration of warp w.
-__host__ __device__ constexpr int chroma_first(int w) {
-    constexpr int LUMA_IT = TILE_MB / 2, CHROMA_IT = TILE_MB / 4, TOTAL = LUMA_IT + CHROMA_IT;
-    int at = 0;
-    for (int i = 0; i < w; i++) {
-        const int luma = LUMA_IT / NWARPS + (i < LUMA_IT % NWARPS ? 1 : 0);
-        int share = (TOTAL + NWARPS - 1) / NWARPS - luma;          // bring warp i up to the even share
-        if (share < 0) share = 0;
-        if (at + share > CHROMA_IT) share = CHROMA_IT - at;
-        at += share;
-    }
-    return w >= NWARPS ? CHROMA_IT : at;
-}
-static_assert(chroma_first(NWARPS) == TILE_MB / 4, "every chroma iteration is handed to some warp");
 
 // ---------------------------------------------------------------- the kernel
 __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncParams P) {
@@ -483,49 +394,76 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
     __syncthreads();
     PHASE_MARK(1);
 
-    // ---- B: colour + DCT + quantise.  8 lanes per PAIR of 8x8 blocks, 4 pairs (8 blocks) per warp per iteration:
-    //      a lane carries row v (then column v) of two blocks in packed f32x2 registers, so every butterfly and
-    //      quantiser operation is one FADD2 / FMUL2 / FFMA2 for both.  Pairs share their pixels: the left and right
-    //      luma block of a macroblock half (one 48-byte row piece), or the Cb and Cr block of a macroblock (the same
-    //      even pixels) — and their chunks are neighbours (types 0/1, 2/3, 4/5), 64 bytes apart.
-    //      A tile is 16 luma iterations (2 macroblocks each) + 8 chroma iterations (4 macroblocks each), four per warp.
+    // ---- B1: colour.  One work item = the 16-pixel (48-byte) piece of an image row that one macroblock covers:
+    //      16 items per macroblock give its luma rows, the 8 even rows once more give its (Cb, Cr) rows.  24 items per
+    //      macroblock, 4 per thread.  Samples leave as bytes, 16 per item: the row of one block next to the row of its
+    //      partner (left | right luma block, Cb | Cr), which is how phase B2 wants them.
+    uint8_t* const samp = S.work;
+    {
+        constexpr int LUMA_ITEMS = TILE_MB * 16, ITEMS = TILE_MB * 24;
+#pragma unroll 1
+        for (int item = tid; item < ITEMS; item += THREADS) {
+            if (item < LUMA_ITEMS) {                 // (warp-uniform: LUMA_ITEMS is a multiple of 32)
+                const int mb = item >> 4, row = item & 15;          // eight consecutive lanes: eight rows of one macroblock, 4 banks apart
+                const uint4* s4 = reinterpret_cast<const uint4*>(S.raw + row * PITCH + mb * 48);
+                const uint4 a = s4[0], b = s4[1], c4 = s4[2];
+                const uint32_t w[12] = { a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w, c4.x, c4.y, c4.z, c4.w };
+                *reinterpret_cast<uint4*>(samp + mb * SAMP_MB + row * 16) = luma_piece(w);
+            } else {
+                const int c = item - LUMA_ITEMS;     // eight consecutive lanes: one row of eight macroblocks (12 banks apart in, 4 out)
+                const int mb = (c & 7) | ((c >> 6) << 3), crow = (c >> 3) & 7;
+                const uint4* s4 = reinterpret_cast<const uint4*>(S.raw + 2 * crow * PITCH + mb * 48);
+                const uint4 a = s4[0], b = s4[1], c4 = s4[2];
+                const uint32_t w[12] = { a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w, c4.x, c4.y, c4.z, c4.w };
+                *reinterpret_cast<uint4*>(samp + mb * SAMP_MB + 256 + crow * 16) = chroma_piece(w);
+            }
+        }
+    }
+    __syncthreads();                                 // samples complete; the pixels are dead from here on
+
+    // ---- B2: DCT + quantise.  8 lanes per PAIR of 8x8 blocks, 4 pairs (8 blocks) per warp per iteration: a lane
+    //      carries row v (then column v) of two blocks in packed f32x2 registers, so every butterfly and quantiser
+    //      operation is one FADD2 / FMUL2 / FFMA2 for both.  A pair's chunks are neighbours (types 0/1, 2/3, 4/5).
+    //      Iterations 0..15 take the luma pairs of two macroblocks each, 16..23 the chroma pairs of four; dealt
+    //      round-robin, every warp gets four (three luma + one chroma, or two + two).
     {
         const int v = lane & 7, jb = lane >> 3;                   // v: my row in pass 1, my column in pass 2
-        // per-lane quantiser constants for natural positions (u, v), u = 0..7, and where
-        // their quantised values go in the chunk
-        float gk[8], gc[8];
-        int pos[8];                                               // scan positions of my 8 coefficients
-#pragma unroll
-        for (int u = 0; u < 8; u++) pos[u] = unscan_rt(8 * u + v);
-        uint8_t* const trg = S.tr[warp] + jb * TR_GROUP + (jb >> 1) * 64 + (jb & 1) * 64;
+        uint8_t* const trg = S.work + SAMP_BYTES + warp * TR_BYTES + jb * TR_GROUP + (jb >> 1) * 64 + (jb & 1) * 64;
         uint4* const tr_row = reinterpret_cast<uint4*>(trg + v * TR_ROW);                        // my row goes out as 4 x 128 bits
         const unsigned long long* const tr_col = reinterpret_cast<const unsigned long long*>(trg + v * 8);   // my column comes back
-        uint8_t* coefb = reinterpret_cast<uint8_t*>(S.coef);
-
-        auto iteration = [&](auto kind, int j) {
-            constexpr bool chroma = decltype(kind)::value;
-            // one ambiguity threshold for every position (the tightest of the table): a few more exact
-            // recomputations, but the per-coefficient test is a running maximum and 8 registers are saved
-            constexpr float gt = chroma ? AWI_GT_MIN_CHROMA : AWI_GT_MIN_LUMA;
-            int mb, type;                                         // type of the pair's first block; the second is type + 1
-            F2 d[8];
-            if (!chroma) {            // macroblock 2j or 2j+1, upper (Y00, Y01) or lower (Y10, Y11) half
-                mb = 2 * j + (jb >> 1);
-                type = (jb & 1) << 1;
-                const uint4* s4 = reinterpret_cast<const uint4*>(S.raw + (((jb & 1) << 3) + v) * PITCH + mb * 48);
-                const uint4 a = s4[0], b = s4[1], c4 = s4[2];
-                const uint32_t w[12] = { a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w, c4.x, c4.y, c4.z, c4.w };
-                luma_row_pair(w, d);
-            } else {                  // (Cb, Cr) of macroblock 4j + jb
-                mb = 4 * j + jb;
-                type = 4;
-                const uint4* s4 = reinterpret_cast<const uint4*>(S.raw + 2 * v * PITCH + mb * 48);
-                const uint4 a = s4[0], b = s4[1], c4 = s4[2];
-                const uint32_t w[12] = { a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w, c4.x, c4.y, c4.z, c4.w };
-                chroma_row_pair(w, d);
+        // per-lane quantiser constants for natural positions (u, v), u = 0..7, and where their quantised values go
+        // in the chunk; reloaded when the warp moves from luma to chroma pairs
+        float gk[8], gc[8];
+        uint32_t pos[8];                             // shared-space address of coefficient (u, v) of chunk 0
+#pragma unroll
+        for (int u = 0; u < 8; u++) pos[u] = smem_addr(S.raw) + (uint32_t) unscan_rt(8 * u + v);
+        int table = -1;
+        constexpr int LUMA_IT = TILE_MB / 2, ALL_IT = LUMA_IT + TILE_MB / 4;
+#pragma unroll 1
+        for (int it = warp; it < ALL_IT; it += NWARPS) {
+            const bool chroma = it >= LUMA_IT;
+            if ((int) chroma != table) {             // (warp-uniform)
+                table = (int) chroma;
+#pragma unroll
+                for (int u = 0; u < 8; u++) { gk[u] = d_gk[table][8 * u + v]; gc[u] = d_gc[table][8 * u + v]; }
             }
+            // macroblock and pair: luma pairs are (Y00, Y01) and (Y10, Y11), chunk types 0 and 2; the chroma pair is type 4
+            const int mb = chroma ? 4 * (it - LUMA_IT) + jb : 2 * it + (jb >> 1);
+            const int type = chroma ? 4 : (jb & 1) << 1;
             const int chunk = mb * 6 + type;
             const bool active = mb < n_mb;
+            F2 d[8];
+            {
+                const uint4 q = *reinterpret_cast<const uint4*>(samp + samp_row(mb, type, v));     // .x/.y block A, .z/.w block B
+                // byte -> float bits 0x4B0000bb (2^23 + b) by one byte permute each; a packed subtraction of 2^23 + 128 centres both
+                const F2 off = f2_splat(8388736.0f);
+#pragma unroll
+                for (int x = 0; x < 8; x++) {
+                    const uint32_t wa = x < 4 ? q.x : q.y, wb = x < 4 ? q.z : q.w;
+                    const uint32_t sel = 0x7440u + (uint32_t) (x & 3);               // 0x4B, 0x00, 0x00, byte x&3 of the word
+                    d[x] = op_sub(f2_pack(__uint_as_float(__byte_perm(wa, 0x4B000000u, sel)), __uint_as_float(__byte_perm(wb, 0x4B000000u, sel))), off);
+                }
+            }
             aan8_t<F2>(d[0], d[1], d[2], d[3], d[4], d[5], d[6], d[7]);           // row pass
             // transpose through shared memory: a row of pairs goes out as four 128-bit stores, a column comes
             // back as eight 64-bit loads (both conflict-free, see TR_ROW)
@@ -542,39 +480,34 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
             for (int u = 0; u < 8; u++) d[u].v = tr_col[u * (TR_ROW / 8)];
             aan8_t<F2>(d[0], d[1], d[2], d[3], d[4], d[5], d[6], d[7]);           // column pass: d[u] = coefficients (u, v) of both blocks
 
-            F2 t[8];
+            // quantise, store (scan order, int8) and keep the largest distance from a rounding boundary
             float dist = 0.0f;
 #pragma unroll
             for (int u = 0; u < 8; u++) {
-                const F2 df = quant_pair(d[u], gk[u], gc[u], t[u]);
-                float e0, e1;
+                F2 t;
+                const F2 df = quant_pair(d[u], gk[u], gc[u], t);
+                float e0, e1, t0, t1;
                 f2_unpack(df, e0, e1);
+                f2_unpack(t, t0, t1);
                 if (u == 0) dist = v == 0 ? 0.0f : fmaxf(fabsf(e0), fabsf(e1));      // the DC (u = v = 0) is exact, never ambiguous
                 else dist = fmaxf(dist, fmaxf(fabsf(e0), fabsf(e1)));
-            }
-            if (active) {
-                uint8_t* cb = coefb + chunk * 64;
-                // lane v = 0 holds the DC position: d[0] there is the exact integer sum of the 64 centred
-                // samples (|S| <= 8192).  It is left as a sum; phase D turns sums into quantised DCs once per
-                // chunk (dct.c:50 + :123 in integers).  The magic add reads the integer without a conversion.
-#pragma unroll
-                for (int u = 0; u < 8; u++) {
-                    float t0, t1;
-                    f2_unpack(t[u], t0, t1);
+                if (active) {
                     if (u == 0 && v == 0) {
+                        // lane v = 0 holds the DC position: d[0] there is the exact integer sum of the 64 centred
+                        // samples (|S| <= 8192).  It is left as a sum; phase D turns sums into quantised DCs once per
+                        // chunk (dct.c:50 + :123 in integers).  The magic add reads the integer without a conversion.
                         float s0, s1;
                         f2_unpack(d[0], s0, s1);
-                        int* dcp = &S.dc[(mb + 1) * 6 + type];
-                        dcp[0] = __float_as_int(s0 + 12582912.0f) - 0x4B400000;
-                        dcp[1] = __float_as_int(s1 + 12582912.0f) - 0x4B400000;
+                        short* dcp = &S.dc[(mb + 1) * 6 + type];
+                        dcp[0] = (short) (__float_as_int(s0 + 12582912.0f) - 0x4B400000);
+                        dcp[1] = (short) (__float_as_int(s1 + 12582912.0f) - 0x4B400000);
                     } else {
-                        uint8_t* q = cb + pos[u];
-                        q[0] = (uint8_t) __float_as_uint(t0);
-                        q[64] = (uint8_t) __float_as_uint(t1);
+                        const uint32_t q = pos[u] + (uint32_t) chunk * 64u;          // the partner's chunk is the next one
+                        asm volatile("st.shared.u8 [%0], %1;\n\tst.shared.u8 [%0+64], %2;" ::"r"(q), "r"(__float_as_uint(t0)), "r"(__float_as_uint(t1)) : "memory");
                     }
                 }
             }
-            const bool mine = active && dist > gt;
+            const bool mine = active && dist > AWI_GT_MIN_LUMA;
             if (__any_sync(0xffffffffu, mine)) {                // rare: remember which coefficients to redo exactly
                 if (mine) {
                     unsigned long long m0 = 0, m1 = 0;
@@ -583,23 +516,16 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
                         if (u > 0 || v > 0) {
                             float x0, x1, tmp;
                             f2_unpack(d[u], x0, x1);
-                            if (quant_absdiff(x0, gk[u], gc[u], tmp) > gt) m0 |= 1ull << (8 * u + v);
-                            if (quant_absdiff(x1, gk[u], gc[u], tmp) > gt) m1 |= 1ull << (8 * u + v);
+                            if (quant_absdiff(x0, gk[u], gc[u], tmp) > AWI_GT_MIN_LUMA) m0 |= 1ull << (8 * u + v);
+                            if (quant_absdiff(x1, gk[u], gc[u], tmp) > AWI_GT_MIN_LUMA) m1 |= 1ull << (8 * u + v);
                         }
                     }
                     // the lane that turns a chunk's mask from zero to non-zero lists the chunk (once)
-                    if (m0 && atomicOr(&S.amb[chunk], m0) == 0ull) S.amb_list[atomicAdd(&S.amb_count, 1)] = (uint16_t) chunk;
-                    if (m1 && atomicOr(&S.amb[chunk + 1], m1) == 0ull) S.amb_list[atomicAdd(&S.amb_count, 1)] = (uint16_t) (chunk + 1);
+                    if (m0 && atomicOr(&S.amb[chunk], m0) == 0ull) S.amb_list[atomicAdd(&S.amb_count, 1)] = (uint8_t) chunk;
+                    if (m1 && atomicOr(&S.amb[chunk + 1], m1) == 0ull) S.amb_list[atomicAdd(&S.amb_count, 1)] = (uint8_t) (chunk + 1);
                 }
             }
-        };
-#pragma unroll
-        for (int u = 0; u < 8; u++) { gk[u] = d_gk[0][8 * u + v]; gc[u] = d_gc[0][8 * u + v]; }
-        for (int j = warp; j < TILE_MB / 2; j += NWARPS) iteration(std::false_type{}, j);
-#pragma unroll
-        for (int u = 0; u < 8; u++) { gk[u] = d_gk[1][8 * u + v]; gc[u] = d_gc[1][8 * u + v]; }
-        // the warps that got one luma iteration less take one chroma iteration more
-        for (int j = chroma_first(warp); j < chroma_first(warp + 1); j++) iteration(std::true_type{}, j);
+        }
     }
 
     PHASE_MARK(2);
@@ -645,14 +571,14 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
             int u = k >> 3, v = k & 7;
             int y = lane >> 2, x0 = (lane & 3) * 2;
             float cyu = __uint_as_float(cos_bits_rt(y * 8 + u));
-            double part = (double) exact_product(sample_of(S, b, y, x0) - 128, cyu, __uint_as_float(cos_bits_rt(x0 * 8 + v)));
-            part += (double) exact_product(sample_of(S, b, y, x0 + 1) - 128, cyu, __uint_as_float(cos_bits_rt((x0 + 1) * 8 + v)));
+            double part = (double) exact_product(sample_of(samp, b, y, x0) - 128, cyu, __uint_as_float(cos_bits_rt(x0 * 8 + v)));
+            part += (double) exact_product(sample_of(samp, b, y, x0 + 1) - 128, cyu, __uint_as_float(cos_bits_rt((x0 + 1) * 8 + v)));
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
             if (lane == 0) {
                 int c = exact_coef_finish(part, u, v);
                 int q = quant_int(c, chroma ? qchroma_rt(k) : qluma_rt(k));
-                reinterpret_cast<int8_t*>(S.coef)[coef_byte(b, unscan_rt(k))] = (int8_t) q;
+                reinterpret_cast<int8_t*>(S.raw)[coef_byte(b, unscan_rt(k))] = (int8_t) q;
             }
         }
     }
@@ -668,7 +594,7 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
         uint32_t w[16];
 #pragma unroll
         for (int q4 = 0; q4 < 4; q4++) {
-            uint4 v = *reinterpret_cast<const uint4*>(&S.coef[coef_word(tid, 4 * q4)]);
+            uint4 v = *reinterpret_cast<const uint4*>(S.raw + coef_byte(tid, 16 * q4));
             w[4 * q4] = v.x; w[4 * q4 + 1] = v.y; w[4 * q4 + 2] = v.z; w[4 * q4 + 3] = v.w;
         }
         uint32_t lo = 0, hi = 0;
@@ -679,16 +605,16 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
             uint32_t nib = ((nz >> 7) * 0x10204080u) >> 28;
             if (i < 8) lo |= nib << (4 * i); else hi |= nib << (4 * (i - 8));
         }
-        const int8_t* cbase = reinterpret_cast<const int8_t*>(S.coef);
+        const int8_t* cbase = reinterpret_cast<const int8_t*>(S.raw);
         auto coef = [&](int i) -> int { return (int) cbase[coef_byte(tid, i)]; };
-        uint32_t* slot = reinterpret_cast<uint32_t*>(S.raw + tid * SLOT);
+        uint32_t* slot = reinterpret_cast<uint32_t*>(S.work + tid * SLOT);
         auto put = [&](int word, uint32_t be) { slot[word] = __byte_perm(be, 0, 0x0123); };
         const int c_dc = dc_coef_from_sum(S.dc[(my_mb + 1) * 6 + my_type]), 
                   c_prev = dc_coef_from_sum(my_mb > 0 ? S.dc[my_mb * 6 + my_type]                  // previous macroblock of the tile
                                                       : (has_halo ? S.halo_sum[my_type] - 128 * 64 : 0));   // or the halo macroblock / frame start
         const int dc = my_type >= 4 ? quant_int(c_dc, 17) : quant_int(c_dc, 16);             // constant divisors
         const int prev = my_type >= 4 ? quant_int(c_prev, 17) : quant_int(c_prev, 16);
-        reinterpret_cast<int8_t*>(S.coef)[coef_byte(tid, 0)] = (int8_t) dc;       // for the optional coefficient output
+        reinterpret_cast<int8_t*>(S.raw)[coef_byte(tid, 0)] = (int8_t) dc;       // for the optional coefficient output
         my_len = (uint32_t) rle_chunk(dc, prev, ((unsigned long long) hi << 32) | lo, coef, put);
     }
 
@@ -717,13 +643,13 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
         if (my_mb < n_mb) {
             uint32_t* dst = reinterpret_cast<uint32_t*>(P.qcoef + ((long long) (tile / P.tiles_per_frame) * (P.mb1 - P.mb0) * 6 + (long long) (mb_first - P.mb0) * 6 + tid) * 64);
 #pragma unroll
-            for (int i = 0; i < 16; i++) dst[i] = S.coef[coef_word(tid, i)];
+            for (int i = 0; i < 16; i++) dst[i] = reinterpret_cast<const uint32_t*>(S.raw)[coef_word(tid, i)];
         }
         __syncthreads();
     }
 
     const bool compact_ok = total + 16 <= (uint32_t) P.compact_cap;   // normally COMPACT_CAP; smaller only under the self-test hook
-    uint8_t* compact = reinterpret_cast<uint8_t*>(S.coef);
+    uint8_t* compact = S.raw;
 
     if (two_pass) {
         // ---- two-pass tail: no tile waits for another.  Reserve room in the staging buffer (16-byte units,
@@ -736,7 +662,7 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
             if ((unsigned long long) at + units > P.stage_cap_units) atomicOr(P.err, 1u);
         }
         if (compact_ok) {
-            const uint8_t* src = S.raw + tid * SLOT;
+            const uint8_t* src = S.work + tid * SLOT;
             uint8_t* dst = compact + my_off;
             for (uint32_t i = 0; i < my_len; i++) dst[i] = src[i];
         }
@@ -754,7 +680,7 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
                 uint4* o4 = reinterpret_cast<uint4*>(out);
                 for (uint32_t j = tid; j < ((total + 15u) >> 4); j += THREADS) o4[j] = c4[j];
             } else {                                     // oversized tile (> 64 B per chunk on average): chunk by chunk
-                const uint8_t* src = S.raw + tid * SLOT;
+                const uint8_t* src = S.work + tid * SLOT;
                 for (uint32_t i = 0; i < my_len; i++) out[my_off + i] = src[i];
             }
         }
@@ -806,7 +732,7 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
     }
     // meanwhile / afterwards: every thread moves its own chunk to its place in the compacted tile
     if (compact_ok) {
-        const uint8_t* src = S.raw + tid * SLOT;
+        const uint8_t* src = S.work + tid * SLOT;
         uint8_t* dst = compact + my_off;
         for (uint32_t i = 0; i < my_len; i++) dst[i] = src[i];
     }
@@ -835,7 +761,7 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
             const uint32_t tail0 = head + (n_words << 2);
             if (tail0 + tid < total) out[tail0 + tid] = compact[tail0 + tid];
         } else if (fits) {                              // oversized tile: chunk by chunk
-            const uint8_t* src = S.raw + tid * SLOT;
+            const uint8_t* src = S.work + tid * SLOT;
             uint8_t* dst = P.out + base + my_off;
             for (uint32_t i = 0; i < my_len; i++) dst[i] = src[i];
         }
