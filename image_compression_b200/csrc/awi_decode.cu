@@ -73,6 +73,8 @@ __device__ __forceinline__ int speculative_len(const uint8_t* s) {
 
 __global__ void __launch_bounds__(256) dec_scan_segments(const uint8_t* __restrict__ payload, unsigned long long P,
                                                          uint8_t* __restrict__ Lg, unsigned long long* __restrict__ table) {
+    pdl_wait();
+    pdl_trigger();
     __shared__ __align__(16) uint8_t s[SEG_STAGE];
     __shared__ uint16_t idx[SEG];            // position -> index in the candidate list (NONE: not a candidate)
     __shared__ uint16_t cand_pos[SEG];       // candidate list, ascending positions
@@ -212,6 +214,8 @@ __global__ void __launch_bounds__(256) dec_scan_segments(const uint8_t* __restri
 __global__ void __launch_bounds__(192) dec_compose(const unsigned long long* __restrict__ in, long long n_in,
                                                    unsigned long long* __restrict__ out,
                                                    unsigned long long* __restrict__ pre) {
+    pdl_wait();
+    pdl_trigger();
     extern __shared__ unsigned long long child_tab[];               // FAN * MAXCH entries
     const long long c0 = (long long) blockIdx.x * FAN, c1 = c0 + FAN < n_in ? c0 + FAN : n_in;
     const int n = (int) (c1 - c0);
@@ -239,6 +243,8 @@ struct NodeState { unsigned long long first_chunk; int entry; int ok; };
 
 __global__ void dec_expand(const unsigned long long* __restrict__ pre, long long n_child,
                            const NodeState* __restrict__ parent, NodeState* __restrict__ child) {
+    pdl_wait();
+    pdl_trigger();
     long long c = (long long) blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= n_child) return;
     NodeState st = parent[c / FAN];
@@ -260,6 +266,8 @@ struct TopLevels {
 };
 __global__ void __launch_bounds__(256) dec_root_expand(const unsigned long long* __restrict__ top_table, TopLevels T,
                                                        unsigned long long expect_chunks, unsigned int* err) {
+    pdl_wait();
+    pdl_trigger();
     if (threadIdx.x == 0) {
         const unsigned long long t = top_table[0];
         NodeState st; st.first_chunk = 0; st.entry = 0; st.ok = 1;
@@ -290,6 +298,8 @@ constexpr int EMIT_SEGS = 32;
 __global__ void __launch_bounds__(256) dec_emit_offsets(const uint8_t* __restrict__ Lg, unsigned long long P,
                                                         const NodeState* __restrict__ seg_state, long long n_seg,
                                                         uint32_t* __restrict__ chunk_off, unsigned long long n_chunks) {
+    pdl_wait();
+    pdl_trigger();
     extern __shared__ __align__(16) uint8_t Ls[];                    // EMIT_SEGS * SEG bytes
     const long long seg0 = (long long) blockIdx.x * EMIT_SEGS;
     const unsigned long long byte0 = (unsigned long long) seg0 * SEG;
@@ -338,6 +348,8 @@ __global__ void __launch_bounds__(DCT_MB) dec_dc_tile(const uint8_t* __restrict_
                                                       int* __restrict__ tile_sum, const int* __restrict__ tile_base,
                                                       int* __restrict__ dcabs, unsigned long long P,
                                                       const unsigned int* __restrict__ err) {
+    pdl_wait();
+    pdl_trigger();
     __shared__ int wsum[DCT_MB / 32][6];
     __shared__ int bsum[DCT_MB / 32][6];
     if (*reinterpret_cast<const volatile unsigned int*>(err) != 0) return;     // boundaries unknown: nothing to scan
@@ -392,6 +404,8 @@ __global__ void __launch_bounds__(DCT_MB) dec_dc_tile(const uint8_t* __restrict_
 // sums are scanned with shuffles)
 __global__ void __launch_bounds__(1024) dec_dc_scan_tiles(const int* __restrict__ tile_sum, long long n_tiles,
                                                           int* __restrict__ tile_base) {
+    pdl_wait();
+    pdl_trigger();
     __shared__ int wtot[32][6];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const long long per = (n_tiles + 1023) / 1024;
@@ -459,6 +473,8 @@ __device__ __forceinline__ void store_px(const DecParams& P, int x, int y, int r
 
 __global__ void __launch_bounds__(REC_THREADS) dec_reconstruct(DecParams P, const uint32_t* __restrict__ chunk_off,
                                                                const int* __restrict__ dcabs, unsigned int* err) {
+    pdl_wait();
+    pdl_trigger();
     extern __shared__ __align__(16) unsigned char smem_raw[];
     RecSmem& S = *reinterpret_cast<RecSmem*>(smem_raw);
     const int tid = threadIdx.x;
@@ -652,7 +668,9 @@ __global__ void __launch_bounds__(REC_THREADS) dec_reconstruct(DecParams P, cons
     }
 }
 
-__global__ void dec_set_word(uint32_t* p, uint32_t v) { *p = v; }
+__global__ void dec_set_word(uint32_t* p, uint32_t v) {
+    pdl_wait();
+    pdl_trigger(); *p = v; }
 
 // ---------------------------------------------------------------- host side
 static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
@@ -729,38 +747,38 @@ cudaError_t launch_decode(const DecParams& P, void* workspace, size_t workspace_
         uint8_t* Lg = ws + Lo.off_L;
         auto table = [&](int lv) { return reinterpret_cast<unsigned long long*>(ws + Lo.off_table[lv]); };
         auto state = [&](int lv) { return reinterpret_cast<NodeState*>(ws + Lo.off_state[lv]); };
-        dec_scan_segments<<<(unsigned) Lo.n_seg, 256, 0, stream>>>(P.payload, P.payload_len, Lg, table(0));
+        launch_pdl(dec_scan_segments, (unsigned) Lo.n_seg, 256, 0, stream, P.payload, P.payload_len, Lg, table(0));
         auto pre = [&](int lv) { return reinterpret_cast<unsigned long long*>(ws + Lo.off_pre[lv]); };
         for (int lv = 1; lv < Lo.levels; lv++)
-            dec_compose<<<(unsigned) Lo.n_node[lv], 192, FAN * MAXCH * 8, stream>>>(table(lv - 1), Lo.n_node[lv - 1], table(lv), pre(lv));
+            launch_pdl(dec_compose, (unsigned) Lo.n_node[lv], 192, FAN * MAXCH * 8, stream, table(lv - 1), Lo.n_node[lv - 1], table(lv), pre(lv));
         TopLevels T{};
         T.levels = Lo.levels;
         for (int lv = 0; lv < Lo.levels; lv++) { T.n_node[lv] = Lo.n_node[lv]; T.pre[lv] = pre(lv); T.state[lv] = state(lv); }
-        dec_root_expand<<<1, 256, 0, stream>>>(table(Lo.levels - 1), T, (unsigned long long) n_chunks, err);
+        launch_pdl(dec_root_expand, 1, 256, 0, stream, table(Lo.levels - 1), T, (unsigned long long) n_chunks, err);
         if (Lo.levels >= 2)
-            dec_expand<<<(unsigned) ((Lo.n_node[0] + 127) / 128), 128, 0, stream>>>(pre(1), Lo.n_node[0], state(1), state(0));
-        dec_emit_offsets<<<(unsigned) ((Lo.n_seg + EMIT_SEGS - 1) / EMIT_SEGS), 256, EMIT_SEGS * SEG, stream>>>(
+            launch_pdl(dec_expand, (unsigned) ((Lo.n_node[0] + 127) / 128), 128, 0, stream, pre(1), Lo.n_node[0], state(1), state(0));
+        launch_pdl(dec_emit_offsets, (unsigned) ((Lo.n_seg + EMIT_SEGS - 1) / EMIT_SEGS), 256, EMIT_SEGS * SEG, stream,
             Lg, P.payload_len, state(0), Lo.n_seg, chunk_off, (unsigned long long) n_chunks);
     } else {
         cudaError_t e = cudaMemcpyAsync(chunk_off, chunk_off_in, (size_t) n_chunks * 4, cudaMemcpyDeviceToDevice, stream);
         if (e != cudaSuccess) return e;
-        dec_set_word<<<1, 1, 0, stream>>>(chunk_off + n_chunks, (uint32_t) P.payload_len);     // the value rides in the launch, no host buffer to outlive
+        launch_pdl(dec_set_word, 1, 1, 0, stream, chunk_off + n_chunks, (uint32_t) P.payload_len);     // the value rides in the launch, no host buffer to outlive
     }
 
     if (!reuse_index) {
-    dec_dc_tile<0><<<(unsigned) Lo.n_dct, DCT_MB, 0, stream>>>(P.payload, chunk_off, n_mb, tile_sum, nullptr, nullptr, P.payload_len, err);
+    launch_pdl(dec_dc_tile<0>, (unsigned) Lo.n_dct, DCT_MB, 0, stream, P.payload, chunk_off, n_mb, tile_sum, nullptr, nullptr, P.payload_len, err);
     if (Lo.n_dct <= 1024) {     // up to 8192x8192: the scan of the tile sums is folded into the second pass
-        dec_dc_tile<2><<<(unsigned) Lo.n_dct, DCT_MB, 0, stream>>>(P.payload, chunk_off, n_mb, nullptr, tile_sum, dcabs, P.payload_len, err);
+        launch_pdl(dec_dc_tile<2>, (unsigned) Lo.n_dct, DCT_MB, 0, stream, P.payload, chunk_off, n_mb, nullptr, tile_sum, dcabs, P.payload_len, err);
     } else {
-        dec_dc_scan_tiles<<<1, 1024, 0, stream>>>(tile_sum, Lo.n_dct, tile_base);
-        dec_dc_tile<1><<<(unsigned) Lo.n_dct, DCT_MB, 0, stream>>>(P.payload, chunk_off, n_mb, nullptr, tile_base, dcabs, P.payload_len, err);
+        launch_pdl(dec_dc_scan_tiles, 1, 1024, 0, stream, tile_sum, Lo.n_dct, tile_base);
+        launch_pdl(dec_dc_tile<1>, (unsigned) Lo.n_dct, DCT_MB, 0, stream, P.payload, chunk_off, n_mb, nullptr, tile_base, dcabs, P.payload_len, err);
     }
     }
 
     const int tiles_per_row = (P.mbw + REC_MB - 1) / REC_MB;
     const int rows = P.mb_row1 - P.mb_row0;
     if (rows > 0)
-        dec_reconstruct<<<(unsigned) (tiles_per_row * rows), REC_THREADS, sizeof(RecSmem), stream>>>(P, chunk_off, dcabs, err);
+        launch_pdl(dec_reconstruct, (unsigned) (tiles_per_row * rows), REC_THREADS, sizeof(RecSmem), stream, P, chunk_off, dcabs, err);
     return cudaGetLastError();
 }
 

@@ -31,6 +31,7 @@
 // GPUs) never wait on each other for data — and in two-pass mode not for the output offset either.
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 #include "codec_math.cuh"
 #include "awi_kernels.h"
 #include <mutex>
@@ -39,46 +40,44 @@
 namespace awi {
 
 #ifndef ENC_MIN_CTAS
-#define ENC_MIN_CTAS 3                           // resident CTAs per SM the register and shared-memory budgets are sized for
+#define ENC_MIN_CTAS 4                           // resident CTAs per SM the register budget is sized for
 #endif
 constexpr int TILE_MB = ENC_TILE_MB;             // 32 macroblocks per tile
-constexpr int NWARPS = 8;                        // every warp owns MB_W consecutive macroblocks from the pixels to the packed chunks
-constexpr int THREADS = NWARPS * 32;
-constexpr int MB_W = TILE_MB / NWARPS;           // 4 macroblocks per warp: 2 + 2 for the two luma iterations, 4 for the chroma one
-constexpr int CH_W = MB_W * 6;                   // 24 chunks per warp: lanes 0..23 code one each
-constexpr int CHUNKS = TILE_MB * 6;
-constexpr int PITCH = TILE_MB * 48 + 16;         // smem bytes per pixel row: 388 words = 4 mod 32 -> eight rows of a
-                                                 // macroblock land 4 banks apart, conflict-free 128-bit row-piece reads
+constexpr int THREADS = TILE_MB * 6;              // = chunks per tile; phase B: 4 blocks at a time per warp, 8 lanes each
+constexpr int NWARPS = THREADS / 32;
+constexpr int PITCH = TILE_MB * 48 + 16;         // smem bytes per pixel row: 388 words = 4 mod 32 -> the 8 rows of a
+                                                 // block land 4 banks apart, conflict-free 64-bit row reads
 constexpr int RAW_BYTES = 16 * PITCH;            // 24832
 constexpr int SLOT = 124;                        // staging bytes per chunk (max 121), 31 words: conflict-free
-constexpr int COEF_BYTES = CHUNKS * 64;          // int8[64] per chunk
-constexpr int SAMP_MB = 400;                     // sample bytes per macroblock: 16 luma pair rows + 8 chroma pair rows of 16 B (+ 16 B spare)
-constexpr int COMPACT_CAP = (RAW_BYTES - 16) & ~15;   // the compacted tile lives in the (dead) pixel buffer: always fits
+constexpr int COEF_BYTES = THREADS * 64;         // int8[64] per chunk
+constexpr int SAMP_MB = 400;                     // sample bytes per macroblock: 16 luma pair rows + 8 chroma pair rows of 16 B, + 16 B so
+                                                 // that macroblocks sit 4 banks apart (eight of them are written side by side)
+constexpr int SAMP_BYTES = TILE_MB * SAMP_MB;    // 12800
+constexpr int COMPACT_CAP = (RAW_BYTES - 16) & ~15;   // the compacted tile lives in the (dead) pixel/coefficient buffer: always fits
 constexpr int TR_ROW = 80;                        // phase B2 transposes, per lane group: 8 rows of 8 (block A, block B) float pairs = 64 B,
 constexpr int TR_GROUP = 8 * TR_ROW;              // rows 80 B apart (20 banks: the eight 128-bit row stores of a group cover all 32 banks),
 constexpr int TR_BYTES = 4 * TR_GROUP + 2 * 64;   // groups 640 B apart, 64 B more in front of groups 1, 2 (carried on) and 3 (the two groups of a half-warp
                                                   // read 64-byte rows 16 banks apart)
-constexpr int WORK_W = MB_W * SAMP_MB + TR_BYTES; // a warp's private scratch: its samples, its transposes; later its chunk slots
-static_assert(TILE_MB % NWARPS == 0 && MB_W == 4, "phase B2 deals 2 + 2 + 4 macroblocks to a warp's three iterations");
-static_assert(CH_W <= 32 && CH_W * SLOT <= WORK_W, "one lane per chunk; the chunk slots alias the warp's samples and transposes");
-static_assert((16 * 3 * TILE_MB) % THREADS == 0, "edge loader: whole passes over the tile's 16-byte pieces");
+static_assert(THREADS == 2 * TILE_MB * 3, "loader: one fixed (macroblock, 16-byte piece) per thread, two rows per pass");
+static_assert(THREADS == TILE_MB * 6, "one thread per chunk in phases D-F");
+static_assert(TILE_MB % 8 == 0 && (TILE_MB * 24) % THREADS == 0, "phase B1: 24 row pieces per macroblock, whole passes");
 
 struct __align__(16) EncSmem {
-    uint8_t raw[RAW_BYTES];                      // phase A-B1: pixels (read-only for every warp); E-F: compacted tile
-    uint8_t work[NWARPS][WORK_W];                // per warp. B1-C: samples; B2: transposes behind them; D-F: chunk slots
-    uint8_t coef[COEF_BYTES];                    // quantised coefficients, int8[64] per chunk, scan order
-    uint8_t halo[16 * 48];                       // macroblock preceding the tile (warp 0)
-    unsigned long long amb[CHUNKS];              // per chunk: natural positions to recompute
-    short dc[(TILE_MB + 1) * 6 + 2];             // block sample sums (the DCs before quantisation), [0..5] = halo macroblock
+    uint8_t raw[RAW_BYTES];                      // phase A-B1: pixels; B2-D: coefficients (int8[64] per chunk, scan order); E-F: compacted tile
+    uint8_t work[SAMP_BYTES + NWARPS * TR_BYTES];   // B1-C: samples [0, SAMP_BYTES), B2: transposes behind them; D-F: chunk slots
+    uint8_t halo[16 * 48];                       // macroblock preceding the tile
+    unsigned long long amb[THREADS];             // per chunk: natural positions to recompute
+    short dc[(TILE_MB + 1) * 6];                 // block sample sums (the DCs before quantisation), [0] = halo macroblock
+    int halo_sum[6];
     uint32_t warp_tot[NWARPS];
-    volatile int dc_ready[NWARPS];               // warp w's sums are in dc[] (the next warp's first macroblock predicts from them)
-    int amb_n[NWARPS];
-    uint8_t amb_list[NWARPS][CH_W];              // a warp's chunks with flagged coefficients
+    uint8_t amb_list[THREADS];                   // chunks with flagged coefficients
+    int amb_count;
     unsigned long long tile_base;
     unsigned long long load_bar;                 // mbarrier the bulk copies of phase A complete on
     int tile;
 };
-static_assert(CHUNKS <= 256, "chunk numbers fit a byte");
+static_assert(THREADS * SLOT <= SAMP_BYTES + NWARPS * TR_BYTES, "chunk slots alias the sample and transpose buffers");
+static_assert(COEF_BYTES <= RAW_BYTES && THREADS <= 256, "coefficients alias the pixel buffer; chunk numbers fit a byte");
 static_assert(sizeof(EncSmem) + 1024 <= (228 * 1024) / ENC_MIN_CTAS, "ENC_MIN_CTAS tiles (+1 KB each the system keeps) must fit an SM's 228 KB");
 
 // chunk index inside the tile: 6*macroblock + type, type 0..3 = Y[i][j], 4 = Cb, 5 = Cr
@@ -286,129 +285,161 @@ __device__ __forceinline__ int sample_of(const uint8_t* samp, int chunk, int y, 
 }
 static_assert(AWI_GT_MIN_LUMA == AWI_GT_MIN_CHROMA, "phase B2 uses one ambiguity threshold for both tables");
 
+#ifdef ENC_PHASE_CLOCKS
+// debug build only (tools/phase_clocks.py): cycles per warp between phase marks, summed over all tiles.
+// Kept in registers and added to one of 128 copies at the end, so the marks do not crowd one L2 slice.
+__device__ unsigned long long g_phase_clk[128][16][8];
+__device__ __forceinline__ long long phase_clock() { long long t; asm volatile("mov.u64 %0, %%clock64;" : "=l"(t) :: "memory"); return t; }
+#define PHASE_INIT() long long t_prev_ = phase_clock(); unsigned int ph_[13] = {}
+#define PHASE_MARK(i) do { long long t_now_ = phase_clock(); ph_[i] = (unsigned int) (t_now_ - t_prev_); t_prev_ = t_now_; \
+        if ((i) == 12 && lane == 0) { for (int q_ = 0; q_ < 13; q_++) atomicAdd(&g_phase_clk[blockIdx.x & 127][q_][warp], (unsigned long long) ph_[q_]); } } while (0)
+extern "C" int awi_debug_phase_clocks(unsigned long long* out, int reset) {
+    static unsigned long long h[128][16][8];
+    if (out) {
+        if (cudaMemcpyFromSymbol(h, g_phase_clk, sizeof(h)) != cudaSuccess) return 0;
+        for (int i = 0; i < 128; i++) out[i] = 0;
+        for (int c = 0; c < 128; c++) for (int i = 0; i < 16; i++) for (int w = 0; w < 8; w++) out[i * 8 + w] += h[c][i][w];
+    }
+    if (reset) { for (auto& c : h) for (auto& r : c) for (auto& v : r) v = 0; if (cudaMemcpyToSymbol(g_phase_clk, h, sizeof(h)) != cudaSuccess) return 0; }
+    return 1;
+}
+#else
+#define PHASE_MARK(i) do { } while (0)
+#define PHASE_INIT() do { } while (0)
+#endif
+
 // ---------------------------------------------------------------- the kernel
 __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncParams P) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     EncSmem& S = *reinterpret_cast<EncSmem*>(smem_raw);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    pdl_wait();                       // the previous step's gather pass is done with the staging buffer and the cursor
+    pdl_trigger();                    // this step's scan/gather pass may take its place on the SMs as they fall free
 
     // single-pass mode: ticketed tile order, so a tile only ever waits on tiles whose CTAs already run.
     // two-pass mode (staging buffer given): tiles are independent, any order will do.
+    PHASE_INIT();
     const bool two_pass = P.stage != nullptr;
-    if (tid == 0) {
-        if (!two_pass) S.tile = (int) atomicAdd(P.ticket, 1u);
-        mbar_init(&S.load_bar, 1);
+    int tile = (int) blockIdx.x;
+    if (!two_pass) {                  // the ticket has to reach every thread: one extra barrier, single-pass mode only
+        if (tid == 0) S.tile = (int) atomicAdd(P.ticket, 1u);
+        __syncthreads();
+        tile = S.tile;
     }
-    if (tid < NWARPS) S.dc_ready[tid] = 0;
-    __syncthreads();                  // barrier 0 of 3: the mbarrier, the flags and the ticket are there for every warp
-    const int tile = two_pass ? (int) blockIdx.x : S.tile;
+    if (tid == 0) S.amb_count = 0;    // (these are first read after the barrier that ends phase A)
+    if (tid < 6) S.halo_sum[tid] = 0;
+    S.amb[tid] = 0;
     // batches: tiles_per_frame tiles per frame, frames frame_stride bytes apart, predictors restart per frame
     const int frame = tile / P.tiles_per_frame, tile_in = tile - frame * P.tiles_per_frame;
     const int mb_first = P.mb0 + tile_in * TILE_MB;              // raster index inside the frame
     const int n_mb = min(TILE_MB, P.mb1 - mb_first);
     const bool has_halo = mb_first > 0;
 
-    // ---- A: stage pixels.  Common case (a full tile of whole macroblocks inside the image, 16-byte aligned rows,
-    //      spanning at most two macroblock rows): every pixel row of the tile is one or two contiguous runs in
-    //      the frame; 16 or 32 lanes of warp 0 ask the copy engine for one run each (cp.async.bulk, bytes counted
-    //      on an mbarrier), and every warp waits on that mbarrier itself: nothing passes through registers, no
-    //      CTA barrier.  Otherwise all threads fetch 16-byte pieces with edge handling (zeros outside the image).
+    // ---- A: stage pixels.  Common case (a full tile of whole macroblocks inside the image, 16-byte aligned
+    //      rows): 16 bulk copies of 1536 contiguous bytes (32 shorter ones where the tile wraps onto the next
+    //      macroblock row), issued by the lanes of warp 0, land in the
+    //      padded rows of S.raw on their own; nothing passes through registers.  Otherwise thread = one
+    //      16-byte piece column (macroblock m, piece k) x 8 rows, with edge handling.
     {
         const uint8_t* const rows = P.rows + (long long) frame * P.frame_stride;
         const int my_first = mb_first / P.mbw, mx_first = mb_first - my_first * P.mbw;
-        const int n_a = min(TILE_MB, P.mbw - mx_first);          // macroblocks on the first macroblock row
+        // a full tile of whole macroblocks inside the image that spans at most two macroblock rows: every pixel row of
+        // the tile is one contiguous run in the frame, or two where the tile wraps onto the next macroblock row
+        const int n_a = min(TILE_MB, P.mbw - mx_first);          // macroblocks of the tile on its first macroblock row
         const bool bulk = P.align == 16 && n_mb == TILE_MB && P.mbw * 16 == P.width && TILE_MB - n_a <= P.mbw &&
                           (my_first + (n_a < TILE_MB ? 2 : 1)) * 16 <= P.height;
-        if (bulk) {
-            if (warp == 0) {
-                if (lane == 0) mbar_arrive_expect(&S.load_bar, 16u * TILE_MB * 48u);
-                __syncwarp();
-                const int r = lane & 15;
-                if (lane < 16) {
-                    const uint8_t* src = rows + (long long) (P.height - 1 - (my_first * 16 + r)) * P.stride + mx_first * 48;
-                    bulk_load(S.raw + r * PITCH, src, (uint32_t) n_a * 48u, &S.load_bar);
-                } else if (n_a < TILE_MB) {                      // the tile wraps onto the next macroblock row
-                    const uint8_t* src = rows + (long long) (P.height - 1 - (my_first * 16 + 16 + r)) * P.stride;
-                    bulk_load(S.raw + r * PITCH + n_a * 48, src, (uint32_t) (TILE_MB - n_a) * 48u, &S.load_bar);
-                }
+        if (bulk && warp == 0) {
+            if (lane == 0) {
+                mbar_init(&S.load_bar, 1);
+                mbar_arrive_expect(&S.load_bar, 16u * TILE_MB * 48u);
             }
-        } else {
-            constexpr int PER = 16 * 3 * TILE_MB / THREADS;      // 6 pieces per thread, all requested before any is stored
-            uint4 v[PER];
-#pragma unroll
-            for (int k = 0; k < PER; k++) {
-                const int p = tid + k * THREADS, row = p / (3 * TILE_MB), col = p - row * (3 * TILE_MB), m = col / 3, kk = col - 3 * m;
-                v[k] = make_uint4(0, 0, 0, 0);
-                if (m < n_mb) {
-                    const int g = mb_first + m, my = g / P.mbw, mx = g - my * P.mbw;
-                    const int xb = mx * 48 + kk * 16, y = my * 16 + row;
-                    if (y < P.height) v[k] = load_piece(rows + (long long) (P.height - 1 - y) * P.stride + xb, P.width * 3 - xb, P.align);
-                }
-            }
-#pragma unroll
-            for (int k = 0; k < PER; k++) {
-                const int p = tid + k * THREADS, row = p / (3 * TILE_MB), col = p - row * (3 * TILE_MB);
-                *reinterpret_cast<uint4*>(S.raw + row * PITCH + col * 16) = v[k];
+            __syncwarp();
+            const int r = lane & 15;
+            if (lane < 16) {
+                const uint8_t* src = rows + (long long) (P.height - 1 - (my_first * 16 + r)) * P.stride + mx_first * 48;
+                bulk_load(S.raw + r * PITCH, src, (uint32_t) n_a * 48u, &S.load_bar);
+            } else if (n_a < TILE_MB) {
+                const uint8_t* src = rows + (long long) (P.height - 1 - (my_first * 16 + 16 + r)) * P.stride;
+                bulk_load(S.raw + r * PITCH + n_a * 48, src, (uint32_t) (TILE_MB - n_a) * 48u, &S.load_bar);
             }
         }
-        // the macroblock in front of the tile (its six block sums seed the DC predictors): warp 0 alone uses it
-        if (warp == 0) {
-            for (int i = lane; i < 48; i += 32) {
-                uint4 h = make_uint4(0, 0, 0, 0);
-                if (has_halo) {
-                    const int g = mb_first - 1, row = i / 3, kk = i - 3 * row;
-                    const int my = g / P.mbw, mx = g - my * P.mbw;
-                    const int xb = mx * 48 + kk * 16, y = my * 16 + row;
-                    if (y < P.height) h = load_piece(rows + (long long) (P.height - 1 - y) * P.stride + xb, P.width * 3 - xb, P.align);
-                }
-                reinterpret_cast<uint4*>(S.halo)[i] = h;
+        const int col = tid % (3 * TILE_MB), m = col / 3, k = col - 3 * m;
+        const int r0 = tid / (3 * TILE_MB);                       // 0 or 1
+        uint4 v[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) v[i] = make_uint4(0, 0, 0, 0);
+        if (!bulk && m < n_mb) {
+            const int g = mb_first + m;
+            const int my = g / P.mbw, mx = g - my * P.mbw;
+            const int xb = mx * 48 + k * 16;
+            const int valid = P.width * 3 - xb;
+            const int y0 = my * 16 + r0;
+            const uint8_t* src = rows + (long long) (P.height - 1 - y0) * P.stride + xb;
+            if (P.align == 16 && valid >= 16 && y0 + 14 < P.height) {     // 8 plain 128-bit loads
+#pragma unroll
+                for (int i = 0; i < 8; i++) v[i] = ld_stream(reinterpret_cast<const uint4*>(src - (long long) (2 * i) * P.stride));
+            } else {
+#pragma unroll
+                for (int i = 0; i < 8; i++)
+                    if (y0 + 2 * i < P.height) v[i] = load_piece(src - (long long) (2 * i) * P.stride, valid, P.align);
             }
         }
-        if (bulk) mbar_wait(&S.load_bar, 0);        // every thread sees the copied bytes once it has seen the phase complete
-        else __syncthreads();                        // (uniform) edge tiles only
+        // the halo macroblock's piece is requested before anything waits on the tile's own loads
+        uint4 h = make_uint4(0, 0, 0, 0);
+        if (tid < 48 && has_halo) {
+            const int g = mb_first - 1, row = tid / 3, kk = tid - 3 * row;
+            const int my = g / P.mbw, mx = g - my * P.mbw;
+            const int xb = mx * 48 + kk * 16, y = my * 16 + row;
+            if (y < P.height)
+                h = load_piece(rows + (long long) (P.height - 1 - y) * P.stride + xb, P.width * 3 - xb, P.align);
+        }
+        if (!bulk) {
+            uint8_t* dst = S.raw + r0 * PITCH + col * 16;
+#pragma unroll
+            for (int i = 0; i < 8; i++) *reinterpret_cast<uint4*>(dst + i * 2 * PITCH) = v[i];
+        }
+        if (tid < 48) reinterpret_cast<uint4*>(S.halo)[tid] = h;
+        if (bulk && warp == 0) mbar_wait(&S.load_bar, 0);          // the barrier below passes the bytes on to the other warps
     }
-
-    // From here to the end of phase D a warp works on its own MB_W macroblocks only: its pixels (read-only, shared),
-    // its scratch S.work[warp], its chunks of S.coef / S.amb / S.dc.  Warps drift apart freely - one warp's
-    // colour arithmetic overlaps another's run-length coding - and meet again at the barrier in front of phase E.
-    uint8_t* const wk = S.work[warp];
-    uint8_t* const samp = wk;                                    // MB_W x SAMP_MB sample bytes
-    const int m0 = warp * MB_W;                                  // my first macroblock in the tile
-    const bool warp_active = m0 < n_mb;
-    if (lane < CH_W) S.amb[warp * CH_W + lane] = 0;
-    if (lane == 0) S.amb_n[warp] = 0;
+    PHASE_MARK(0);
+    __syncthreads();
+    PHASE_MARK(1);
 
     // ---- B1: colour.  One work item = the 16-pixel (48-byte) piece of an image row that one macroblock covers:
-    //      16 items per macroblock give its luma rows, the 8 even rows once more give its (Cb, Cr) rows: 96 items,
-    //      3 per lane.  Samples leave as bytes, 16 per item: the row of one block next to the row of its partner
-    //      (left | right luma block, Cb | Cr), which is how phase B2 wants them.
-    if (warp_active) {
+    //      16 items per macroblock give its luma rows, the 8 even rows once more give its (Cb, Cr) rows.  24 items per
+    //      macroblock, 4 per thread.  Samples leave as bytes, 16 per item: the row of one block next to the row of its
+    //      partner (left | right luma block, Cb | Cr), which is how phase B2 wants them.
+    uint8_t* const samp = S.work;
+    {
+        constexpr int LUMA_ITEMS = TILE_MB * 16, ITEMS = TILE_MB * 24;
 #pragma unroll 1
-        for (int pass = 0; pass < 3; pass++) {
-            if (pass < 2) {
-                const int ml = 2 * pass + (lane >> 4), row = lane & 15;       // eight consecutive lanes: eight rows of one macroblock, 4 banks apart
-                const uint4* s4 = reinterpret_cast<const uint4*>(S.raw + row * PITCH + (m0 + ml) * 48);
+        for (int item = tid; item < ITEMS; item += THREADS) {
+            if (item < LUMA_ITEMS) {                 // (warp-uniform: LUMA_ITEMS is a multiple of 32)
+                const int mb = item >> 4, row = item & 15;          // eight consecutive lanes: eight rows of one macroblock, 4 banks apart
+                const uint4* s4 = reinterpret_cast<const uint4*>(S.raw + row * PITCH + mb * 48);
                 const uint4 a = s4[0], b = s4[1], c4 = s4[2];
                 const uint32_t w[12] = { a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w, c4.x, c4.y, c4.z, c4.w };
-                *reinterpret_cast<uint4*>(samp + ml * SAMP_MB + row * 16) = luma_piece(w);
+                *reinterpret_cast<uint4*>(samp + mb * SAMP_MB + row * 16) = luma_piece(w);
             } else {
-                const int ml = lane >> 3, crow = lane & 7;
-                const uint4* s4 = reinterpret_cast<const uint4*>(S.raw + 2 * crow * PITCH + (m0 + ml) * 48);
+                const int c = item - LUMA_ITEMS;     // eight consecutive lanes: one row of eight macroblocks (12 banks apart in, 4 out)
+                const int mb = (c & 7) | ((c >> 6) << 3), crow = (c >> 3) & 7;
+                const uint4* s4 = reinterpret_cast<const uint4*>(S.raw + 2 * crow * PITCH + mb * 48);
                 const uint4 a = s4[0], b = s4[1], c4 = s4[2];
                 const uint32_t w[12] = { a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w, c4.x, c4.y, c4.z, c4.w };
-                *reinterpret_cast<uint4*>(samp + ml * SAMP_MB + 256 + crow * 16) = chroma_piece(w);
+                *reinterpret_cast<uint4*>(samp + mb * SAMP_MB + 256 + crow * 16) = chroma_piece(w);
             }
         }
     }
-    __syncwarp();
+    __syncthreads();                                 // samples complete; the pixels are dead from here on
 
-    // ---- B2: DCT + quantise.  8 lanes per PAIR of 8x8 blocks, 4 pairs (8 blocks) per iteration: a lane carries
-    //      row v (then column v) of two blocks in packed f32x2 registers, so every butterfly and quantiser
+    // ---- B2: DCT + quantise.  8 lanes per PAIR of 8x8 blocks, 4 pairs (8 blocks) per warp per iteration: a lane
+    //      carries row v (then column v) of two blocks in packed f32x2 registers, so every butterfly and quantiser
     //      operation is one FADD2 / FMUL2 / FFMA2 for both.  A pair's chunks are neighbours (types 0/1, 2/3, 4/5).
-    //      Iterations 0 and 1 take the luma pairs of two macroblocks each, iteration 2 the chroma pairs of all four.
-    if (warp_active) {
+    //      Iterations 0..15 take the luma pairs of two macroblocks each, 16..23 the chroma pairs of four; dealt
+    //      round-robin, every warp gets four (three luma + one chroma, or two + two).
+    {
         const int v = lane & 7, jb = lane >> 3;                   // v: my row in pass 1, my column in pass 2
-        uint8_t* const trg = wk + MB_W * SAMP_MB + jb * TR_GROUP + (jb >> 1) * 64 + (jb & 1) * 64;
+        uint8_t* const trg = S.work + SAMP_BYTES + warp * TR_BYTES + jb * TR_GROUP + (jb >> 1) * 64 + (jb & 1) * 64;
         uint4* const tr_row = reinterpret_cast<uint4*>(trg + v * TR_ROW);                        // my row goes out as 4 x 128 bits
         const unsigned long long* const tr_col = reinterpret_cast<const unsigned long long*>(trg + v * 8);   // my column comes back
         // per-lane quantiser constants for natural positions (u, v), u = 0..7, and where their quantised values go
@@ -416,22 +447,25 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
         float gk[8], gc[8];
         uint32_t pos[8];                             // shared-space address of coefficient (u, v) of chunk 0
 #pragma unroll
-        for (int u = 0; u < 8; u++) pos[u] = smem_addr(S.coef) + (uint32_t) unscan_rt(8 * u + v);
+        for (int u = 0; u < 8; u++) pos[u] = smem_addr(S.raw) + (uint32_t) unscan_rt(8 * u + v);
+        int table = -1;
+        constexpr int LUMA_IT = TILE_MB / 2, ALL_IT = LUMA_IT + TILE_MB / 4;
 #pragma unroll 1
-        for (int it = 0; it < 3; it++) {
-            const bool chroma = it == 2;
-            if (it != 1) {                           // (uniform)
+        for (int it = warp; it < ALL_IT; it += NWARPS) {
+            const bool chroma = it >= LUMA_IT;
+            if ((int) chroma != table) {             // (warp-uniform)
+                table = (int) chroma;
 #pragma unroll
-                for (int u = 0; u < 8; u++) { gk[u] = d_gk[chroma][8 * u + v]; gc[u] = d_gc[chroma][8 * u + v]; }
+                for (int u = 0; u < 8; u++) { gk[u] = d_gk[table][8 * u + v]; gc[u] = d_gc[table][8 * u + v]; }
             }
             // macroblock and pair: luma pairs are (Y00, Y01) and (Y10, Y11), chunk types 0 and 2; the chroma pair is type 4
-            const int ml = chroma ? jb : 2 * it + (jb >> 1);
+            const int mb = chroma ? 4 * (it - LUMA_IT) + jb : 2 * it + (jb >> 1);
             const int type = chroma ? 4 : (jb & 1) << 1;
-            const int chunk = (m0 + ml) * 6 + type;
-            const bool active = m0 + ml < n_mb;
+            const int chunk = mb * 6 + type;
+            const bool active = mb < n_mb;
             F2 d[8];
             {
-                const uint4 q = *reinterpret_cast<const uint4*>(samp + samp_row(ml, type, v));     // .x/.y block A, .z/.w block B
+                const uint4 q = *reinterpret_cast<const uint4*>(samp + samp_row(mb, type, v));     // .x/.y block A, .z/.w block B
                 // byte -> float bits 0x4B0000bb (2^23 + b) by one byte permute each; a packed subtraction of 2^23 + 128 centres both
                 const F2 off = f2_splat(8388736.0f);
 #pragma unroll
@@ -475,7 +509,7 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
                         // chunk (dct.c:50 + :123 in integers).  The magic add reads the integer without a conversion.
                         float s0, s1;
                         f2_unpack(d[0], s0, s1);
-                        short* dcp = &S.dc[(m0 + ml + 1) * 6 + type];
+                        short* dcp = &S.dc[(mb + 1) * 6 + type];
                         dcp[0] = (short) (__float_as_int(s0 + 12582912.0f) - 0x4B400000);
                         dcp[1] = (short) (__float_as_int(s1 + 12582912.0f) - 0x4B400000);
                     } else {
@@ -487,98 +521,91 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
             const bool mine = active && dist > AWI_GT_MIN_LUMA;
             if (__any_sync(0xffffffffu, mine)) {                // rare: remember which coefficients to redo exactly
                 if (mine) {
-                    unsigned long long m0_ = 0, m1_ = 0;
+                    unsigned long long m0 = 0, m1 = 0;
 #pragma unroll
                     for (int u = 0; u < 8; u++) {
                         if (u > 0 || v > 0) {
                             float x0, x1, tmp;
                             f2_unpack(d[u], x0, x1);
-                            if (quant_absdiff(x0, gk[u], gc[u], tmp) > AWI_GT_MIN_LUMA) m0_ |= 1ull << (8 * u + v);
-                            if (quant_absdiff(x1, gk[u], gc[u], tmp) > AWI_GT_MIN_LUMA) m1_ |= 1ull << (8 * u + v);
+                            if (quant_absdiff(x0, gk[u], gc[u], tmp) > AWI_GT_MIN_LUMA) m0 |= 1ull << (8 * u + v);
+                            if (quant_absdiff(x1, gk[u], gc[u], tmp) > AWI_GT_MIN_LUMA) m1 |= 1ull << (8 * u + v);
                         }
                     }
                     // the lane that turns a chunk's mask from zero to non-zero lists the chunk (once)
-                    if (m0_ && atomicOr(&S.amb[chunk], m0_) == 0ull) S.amb_list[warp][atomicAdd(&S.amb_n[warp], 1)] = (uint8_t) chunk;
-                    if (m1_ && atomicOr(&S.amb[chunk + 1], m1_) == 0ull) S.amb_list[warp][atomicAdd(&S.amb_n[warp], 1)] = (uint8_t) (chunk + 1);
+                    if (m0 && atomicOr(&S.amb[chunk], m0) == 0ull) S.amb_list[atomicAdd(&S.amb_count, 1)] = (uint8_t) chunk;
+                    if (m1 && atomicOr(&S.amb[chunk + 1], m1) == 0ull) S.amb_list[atomicAdd(&S.amb_count, 1)] = (uint8_t) (chunk + 1);
                 }
             }
         }
     }
-    __syncwarp();
-    // my macroblocks' block sums are in S.dc: the next warp may read the last one's
-    if (lane == 0) { __threadfence_block(); S.dc_ready[warp] = 1; }
 
-    // halo macroblock (warp 0): only its six block sums are needed (integer DC formula).  Lane = (pixel row, half):
-    // eight pixels of one luma block; on even rows also four chroma samples.
-    if (warp == 0 && has_halo) {
-        const int row = lane >> 1, h8 = (lane & 1) * 8;
-        const uint8_t* q = S.halo + row * 48 + h8 * 3;
-        int sy = 0, scb = 0, scr = 0;
+    PHASE_MARK(2);
+    // halo macroblock: only the six block sums are needed (integer DC formula)
+    if (has_halo) {
+        // 192 work items in whole warps: 128 pixel pairs for the four luma sums, 64 pixels for the two chroma sums
+        for (int item = tid; item < 192; item += THREADS) {
+            if (item < 128) {
+                int p = 2 * item, py = p >> 4, px = p & 15;
+                const uint8_t* q = S.halo + py * 48 + px * 3;
+                int s = luma_of(q[2], q[1], q[0]) + luma_of(q[5], q[4], q[3]);
+                s += __shfl_xor_sync(0xffffffffu, s, 1);
+                s += __shfl_xor_sync(0xffffffffu, s, 2);
+                s += __shfl_xor_sync(0xffffffffu, s, 8);
+                s += __shfl_xor_sync(0xffffffffu, s, 16);
+                if ((lane & 27) == 0) atomicAdd(&S.halo_sum[((py >> 3) << 1) | (px >> 3)], s);
+            } else {
+                int t = item - 128, yy = t >> 3, xx = t & 7;
+                const uint8_t* q = S.halo + 2 * yy * 48 + 6 * xx;
+                int cb = chroma_of(q[2], q[1], q[0], false), cr = chroma_of(q[2], q[1], q[0], true);
 #pragma unroll
-        for (int x = 0; x < 8; x++) sy += luma_of(q[3 * x + 2], q[3 * x + 1], q[3 * x]);
-        if ((row & 1) == 0) {
-#pragma unroll
-            for (int x = 0; x < 8; x += 2) {
-                scb += chroma_of(q[3 * x + 2], q[3 * x + 1], q[3 * x], false);
-                scr += chroma_of(q[3 * x + 2], q[3 * x + 1], q[3 * x], true);
-            }
-        }
-        // luma block of a lane: (row >> 3, half) = lane bits 4 and 0: add up over lane bits 1..3
-#pragma unroll
-        for (int o = 2; o <= 8; o <<= 1) sy += __shfl_xor_sync(0xffffffffu, sy, o);
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            scb += __shfl_xor_sync(0xffffffffu, scb, o);
-            scr += __shfl_xor_sync(0xffffffffu, scr, o);
-        }
-        if ((lane & 14) == 0) S.dc[((lane >> 4) << 1) | (lane & 1)] = (short) (sy - 128 * 64);
-        if (lane == 0) { S.dc[4] = (short) (scb - 128 * 64); S.dc[5] = (short) (scr - 128 * 64); }
-    }
-    __syncwarp();
-
-    // ---- C: exact recomputation of my flagged coefficients (dct.c:26-53 operation order), the whole warp per coefficient
-    {
-        const int n_amb = S.amb_n[warp];
-        for (int e = 0; e < n_amb; e++) {
-            const int b = S.amb_list[warp][e];
-            unsigned long long m = S.amb[b];
-            const bool chroma = (b % 6) >= 4;
-            const int bl = b - m0 * 6;                                   // chunk number inside my samples
-            while (m) {
-                int k = __ffsll((long long) m) - 1;
-                m &= m - 1;
-                int u = k >> 3, v = k & 7;
-                int y = lane >> 2, x0 = (lane & 3) * 2;
-                float cyu = __uint_as_float(cos_bits_rt(y * 8 + u));
-                double part = (double) exact_product(sample_of(samp, bl, y, x0) - 128, cyu, __uint_as_float(cos_bits_rt(x0 * 8 + v)));
-                part += (double) exact_product(sample_of(samp, bl, y, x0 + 1) - 128, cyu, __uint_as_float(cos_bits_rt((x0 + 1) * 8 + v)));
-#pragma unroll
-                for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
-                if (lane == 0) {
-                    int c = exact_coef_finish(part, u, v);
-                    int q = quant_int(c, chroma ? qchroma_rt(k) : qluma_rt(k));
-                    reinterpret_cast<int8_t*>(S.coef)[coef_byte(b, unscan_rt(k))] = (int8_t) q;
+                for (int o = 16; o > 0; o >>= 1) {
+                    cb += __shfl_xor_sync(0xffffffffu, cb, o);
+                    cr += __shfl_xor_sync(0xffffffffu, cr, o);
                 }
+                if (lane == 0) { atomicAdd(&S.halo_sum[4], cb); atomicAdd(&S.halo_sum[5], cr); }
             }
         }
     }
-    __syncwarp();                                      // fix-ups landed; samples and transposes are dead: the slots take their place
+    PHASE_MARK(3);
+    __syncthreads();
+    PHASE_MARK(4);
 
-    // ---- D: run-length + bit packing, lane = chunk (24 of a warp's 32 lanes), into its slot
+    // ---- C: exact recomputation of flagged coefficients (dct.c:26-53 operation order)
+    const int n_amb = S.amb_count;
+    for (int e = warp; e < n_amb; e += NWARPS) {
+        const int b = S.amb_list[e];
+        unsigned long long m = S.amb[b];
+        const bool chroma = (b % 6) >= 4;
+        while (m) {
+            int k = __ffsll((long long) m) - 1;
+            m &= m - 1;
+            int u = k >> 3, v = k & 7;
+            int y = lane >> 2, x0 = (lane & 3) * 2;
+            float cyu = __uint_as_float(cos_bits_rt(y * 8 + u));
+            double part = (double) exact_product(sample_of(samp, b, y, x0) - 128, cyu, __uint_as_float(cos_bits_rt(x0 * 8 + v)));
+            part += (double) exact_product(sample_of(samp, b, y, x0 + 1) - 128, cyu, __uint_as_float(cos_bits_rt((x0 + 1) * 8 + v)));
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+            if (lane == 0) {
+                int c = exact_coef_finish(part, u, v);
+                int q = quant_int(c, chroma ? qchroma_rt(k) : qluma_rt(k));
+                reinterpret_cast<int8_t*>(S.raw)[coef_byte(b, unscan_rt(k))] = (int8_t) q;
+            }
+        }
+    }
+    PHASE_MARK(5);
+    if (n_amb > 0) __syncthreads();                    // (uniform) the fix-ups land before phase D; without any, the
+                                                       // barrier after phase B already separates the raw pixels from the slots
+
+    PHASE_MARK(6);
+    // ---- D: run-length + bit packing, thread = chunk, into its slot
     uint32_t my_len = 0;
-    const int my_chunk = warp * CH_W + lane;             // chunk number inside the tile (lanes 0..23)
-    const int my_mb = m0 + lane / 6, my_type = lane % 6;
-    const bool my_valid = lane < CH_W && my_mb < n_mb;
-    if (warp > 0 && warp_active) {                       // my first macroblock predicts from the previous warp's last one
-        if (lane == 0) while (S.dc_ready[warp - 1] == 0) { }
-        __syncwarp();
-        __threadfence_block();
-    }
-    if (my_valid) {
+    const int my_mb = tid / 6, my_type = tid - 6 * my_mb;
+    if (my_mb < n_mb) {
         uint32_t w[16];
 #pragma unroll
         for (int q4 = 0; q4 < 4; q4++) {
-            uint4 v = *reinterpret_cast<const uint4*>(S.coef + coef_byte(my_chunk, 16 * q4));
+            uint4 v = *reinterpret_cast<const uint4*>(S.raw + coef_byte(tid, 16 * q4));
             w[4 * q4] = v.x; w[4 * q4 + 1] = v.y; w[4 * q4 + 2] = v.z; w[4 * q4 + 3] = v.w;
         }
         uint32_t lo = 0, hi = 0;
@@ -589,26 +616,20 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
             uint32_t nib = ((nz >> 7) * 0x10204080u) >> 28;
             if (i < 8) lo |= nib << (4 * i); else hi |= nib << (4 * (i - 8));
         }
-        const int8_t* cbase = reinterpret_cast<const int8_t*>(S.coef);
-        auto coef = [&](int i) -> int { return (int) cbase[coef_byte(my_chunk, i)]; };
-        uint32_t* slot = reinterpret_cast<uint32_t*>(wk + lane * SLOT);
+        const int8_t* cbase = reinterpret_cast<const int8_t*>(S.raw);
+        auto coef = [&](int i) -> int { return (int) cbase[coef_byte(tid, i)]; };
+        uint32_t* slot = reinterpret_cast<uint32_t*>(S.work + tid * SLOT);
         auto put = [&](int word, uint32_t be) { slot[word] = __byte_perm(be, 0, 0x0123); };
-        // S.dc[6 * (mb + 1) + type] = sum of macroblock mb, so the predecessor's sits at 6 * mb + type ([0..5]: the halo macroblock)
-        const volatile short* dcv = S.dc;
-        const int c_dc = dc_coef_from_sum(dcv[(my_mb + 1) * 6 + my_type]),
-                  c_prev = (my_mb > 0 || has_halo) ? dc_coef_from_sum(dcv[my_mb * 6 + my_type]) : 0;      // frame start: predictors are 0
+        const int c_dc = dc_coef_from_sum(S.dc[(my_mb + 1) * 6 + my_type]), 
+                  c_prev = dc_coef_from_sum(my_mb > 0 ? S.dc[my_mb * 6 + my_type]                  // previous macroblock of the tile
+                                                      : (has_halo ? S.halo_sum[my_type] - 128 * 64 : 0));   // or the halo macroblock / frame start
         const int dc = my_type >= 4 ? quant_int(c_dc, 17) : quant_int(c_dc, 16);             // constant divisors
         const int prev = my_type >= 4 ? quant_int(c_prev, 17) : quant_int(c_prev, 16);
-        reinterpret_cast<int8_t*>(S.coef)[coef_byte(my_chunk, 0)] = (int8_t) dc;       // for the optional coefficient output
+        reinterpret_cast<int8_t*>(S.raw)[coef_byte(tid, 0)] = (int8_t) dc;       // for the optional coefficient output
         my_len = (uint32_t) rle_chunk(dc, prev, ((unsigned long long) hi << 32) | lo, coef, put);
-        if (P.qcoef != nullptr) {                        // optional per-chunk output (tests)
-            uint32_t* dst = reinterpret_cast<uint32_t*>(P.qcoef + ((long long) (tile / P.tiles_per_frame) * (P.mb1 - P.mb0) * 6 + (long long) (mb_first - P.mb0) * 6 + my_chunk) * 64);
-            const uint32_t* src = reinterpret_cast<const uint32_t*>(S.coef + coef_byte(my_chunk, 0));
-#pragma unroll
-            for (int i = 0; i < 16; i++) dst[i] = src[i];
-        }
     }
 
+    PHASE_MARK(7);
     // ---- E: offsets inside the tile
     uint32_t total, my_off;
     {
@@ -619,13 +640,25 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
             if (lane >= o) incl += t;
         }
         if (lane == 31) S.warp_tot[warp] = incl;
-        __syncthreads();                                // barrier 1 of 3: every warp is through phase D; the pixels are dead
+        PHASE_MARK(8);
+        __syncthreads();                                // also: every slot written, coefficients no longer read by D
         uint32_t wbase = 0;
         total = 0;
 #pragma unroll
         for (int i = 0; i < NWARPS; i++) { uint32_t t = S.warp_tot[i]; if (i < warp) wbase += t; total += t; }
         my_off = wbase + incl - my_len;
     }
+    PHASE_MARK(9);
+    // optional per-chunk outputs (tests, decode side-info) need the coefficient buffer: before it is reused
+    if (P.qcoef != nullptr) {
+        if (my_mb < n_mb) {
+            uint32_t* dst = reinterpret_cast<uint32_t*>(P.qcoef + ((long long) (tile / P.tiles_per_frame) * (P.mb1 - P.mb0) * 6 + (long long) (mb_first - P.mb0) * 6 + tid) * 64);
+#pragma unroll
+            for (int i = 0; i < 16; i++) dst[i] = reinterpret_cast<const uint32_t*>(S.raw)[coef_word(tid, i)];
+        }
+        __syncthreads();
+    }
+
     const bool compact_ok = total + 16 <= (uint32_t) P.compact_cap;   // normally COMPACT_CAP; smaller only under the self-test hook
     uint8_t* compact = S.raw;
 
@@ -640,15 +673,17 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
             if ((unsigned long long) at + units > P.stage_cap_units) atomicOr(P.err, 1u);
         }
         if (compact_ok) {
-            const uint8_t* src = wk + lane * SLOT;
+            const uint8_t* src = S.work + tid * SLOT;
             uint8_t* dst = compact + my_off;
             for (uint32_t i = 0; i < my_len; i++) dst[i] = src[i];
         }
+        PHASE_MARK(10);
         __syncthreads();
+        PHASE_MARK(11);
         const unsigned long long at = S.tile_base;
         const bool fits = at + ((total + 15u) >> 4) <= P.stage_cap_units;
-        if (P.chunk_off != nullptr && my_valid)
-            P.chunk_off[(long long) (tile / P.tiles_per_frame) * (P.mb1 - P.mb0) * 6 + (long long) (mb_first - P.mb0) * 6 + my_chunk] = my_off;          // tile-relative; the gather pass adds the tile's offset
+        if (P.chunk_off != nullptr && my_mb < n_mb)
+            P.chunk_off[(long long) (tile / P.tiles_per_frame) * (P.mb1 - P.mb0) * 6 + (long long) (mb_first - P.mb0) * 6 + tid] = my_off;          // tile-relative; the gather pass adds the tile's offset
         if (fits) {
             uint8_t* out = P.stage + at * 16;
             if (compact_ok) {
@@ -656,10 +691,11 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
                 uint4* o4 = reinterpret_cast<uint4*>(out);
                 for (uint32_t j = tid; j < ((total + 15u) >> 4); j += THREADS) o4[j] = c4[j];
             } else {                                     // oversized tile (> 64 B per chunk on average): chunk by chunk
-                const uint8_t* src = wk + lane * SLOT;
+                const uint8_t* src = S.work + tid * SLOT;
                 for (uint32_t i = 0; i < my_len; i++) out[my_off + i] = src[i];
             }
         }
+        PHASE_MARK(12);
         return;
     }
 
@@ -707,7 +743,7 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
     }
     // meanwhile / afterwards: every thread moves its own chunk to its place in the compacted tile
     if (compact_ok) {
-        const uint8_t* src = wk + lane * SLOT;
+        const uint8_t* src = S.work + tid * SLOT;
         uint8_t* dst = compact + my_off;
         for (uint32_t i = 0; i < my_len; i++) dst[i] = src[i];
     }
@@ -718,8 +754,8 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
         const unsigned long long base = S.tile_base;
         const bool fits = base + total <= P.out_cap;
         if (!fits && tid == 0) atomicOr(P.err, 1u);
-        if (P.chunk_off != nullptr && my_valid)
-            P.chunk_off[(long long) (tile / P.tiles_per_frame) * (P.mb1 - P.mb0) * 6 + (long long) (mb_first - P.mb0) * 6 + my_chunk] = (uint32_t) (base + my_off);
+        if (P.chunk_off != nullptr && my_mb < n_mb)
+            P.chunk_off[(long long) (tile / P.tiles_per_frame) * (P.mb1 - P.mb0) * 6 + (long long) (mb_first - P.mb0) * 6 + tid] = (uint32_t) (base + my_off);
         if (fits && compact_ok) {
             uint8_t* out = P.out + base;
             const uint32_t head = min(total, (uint32_t) ((4 - (reinterpret_cast<uintptr_t>(out) & 3)) & 3));
@@ -736,7 +772,7 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
             const uint32_t tail0 = head + (n_words << 2);
             if (tail0 + tid < total) out[tail0 + tid] = compact[tail0 + tid];
         } else if (fits) {                              // oversized tile: chunk by chunk
-            const uint8_t* src = wk + lane * SLOT;
+            const uint8_t* src = S.work + tid * SLOT;
             uint8_t* dst = P.out + base + my_off;
             for (uint32_t i = 0; i < my_len; i++) dst[i] = src[i];
         }
@@ -756,6 +792,8 @@ __global__ void __launch_bounds__(1024) enc_scan_tiles(const uint2* __restrict__
                                                        unsigned int* __restrict__ stage_cursor) {
     __shared__ unsigned long long wsum[32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    pdl_wait();
+    pdl_trigger();
     const int per = ((n_tiles + 31) / 32 + 31) & ~31;               // tiles per warp, a multiple of 32
     const int t0 = min(n_tiles, warp * per), t1 = min(n_tiles, t0 + per);
     unsigned long long mine = 0;
@@ -807,6 +845,8 @@ __global__ void __launch_bounds__(256) enc_gather_tiles(const uint8_t* __restric
                                                         unsigned long long* __restrict__ frame_off,
                                                         unsigned long long stage_cap_units) {
     const int tile = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    pdl_wait();
+    pdl_trigger();
     if (tile >= n_tiles || *out_len > out_cap) return;
     const uint2 info = tile_info[tile];
     if ((unsigned long long) info.x + ((info.y + 15u) >> 4) > stage_cap_units) return;   // never staged (err bit 0 is already set)
@@ -853,6 +893,8 @@ __global__ void __launch_bounds__(256) enc_scan_gather_tiles(const uint8_t* __re
                                                              unsigned long long stage_cap_units) {
     __shared__ unsigned long long wsum[8];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    pdl_wait();                       // every tile of the encode kernel is staged and recorded
+    pdl_trigger();
     const int first = blockIdx.x * 8;
     unsigned long long mine = 0;
     for (int t = tid; t < first; t += 256) mine += tile_info[t].y;
@@ -913,6 +955,11 @@ __global__ void __launch_bounds__(256) enc_scan_gather_tiles(const uint8_t* __re
 // ---------------------------------------------------------------- launch
 size_t enc_smem_bytes() { return sizeof(EncSmem); }
 
+bool pdl_enabled() {
+    static const bool on = getenv("GPU_CODEC_NO_PDL") == nullptr;
+    return on;
+}
+
 cudaError_t launch_encode(const EncParams& P, int n_tiles, cudaStream_t stream) {
     static bool attr_set[64] = { false };
     static std::mutex attr_mu;                       // contexts of several devices may launch from different host threads
@@ -933,22 +980,23 @@ cudaError_t launch_encode(const EncParams& P, int n_tiles, cudaStream_t stream) 
     Q.n_tiles = n_tiles;
     if (Q.compact_cap <= 0 || Q.compact_cap > COMPACT_CAP) Q.compact_cap = COMPACT_CAP;
     if (Q.tiles_per_frame <= 0) { Q.tiles_per_frame = n_tiles; Q.frame_stride = 0; }      // a single frame
-    awi_encode_kernel<<<n_tiles, THREADS, sizeof(EncSmem), stream>>>(Q);
+    cudaError_t le = launch_pdl(awi_encode_kernel, (unsigned) n_tiles, THREADS, sizeof(EncSmem), stream, Q);
+    if (le != cudaSuccess) return le;
     if (P.stage != nullptr) {
         if (n_tiles <= ENC_FUSED_MAX_TILES) {
-            enc_scan_gather_tiles<<<(n_tiles + 7) / 8, 256, 0, stream>>>(P.stage, P.tile_info, n_tiles, P.out, P.out_len, P.out_len_user,
+            le = launch_pdl(enc_scan_gather_tiles, (unsigned) (n_tiles + 7) / 8, 256, 0, stream, P.stage, P.tile_info, n_tiles, P.out, P.out_len, P.out_len_user,
                                                                          P.chain_in, P.chain_out, P.out_cap, P.err, P.stage_cursor,
                                                                          P.chunk_off, Q.tiles_per_frame, (P.mb1 - P.mb0) * 6, P.frame_off,
                                                                          P.stage_cap_units);
         } else {
-            enc_scan_tiles<<<1, 1024, 0, stream>>>(P.tile_info, n_tiles, P.tile_off, P.out_len, P.chain_in, P.chain_out, P.out_cap, P.err,
+            le = launch_pdl(enc_scan_tiles, 1, 1024, 0, stream, P.tile_info, n_tiles, P.tile_off, P.out_len, P.chain_in, P.chain_out, P.out_cap, P.err,
                                                    P.out_len_user, P.stage_cursor);
-            enc_gather_tiles<<<(n_tiles + 7) / 8, 256, 0, stream>>>(P.stage, P.tile_info, P.tile_off, n_tiles, P.out, P.out_len,
+            if (le == cudaSuccess) le = launch_pdl(enc_gather_tiles, (unsigned) (n_tiles + 7) / 8, 256, 0, stream, P.stage, P.tile_info, P.tile_off, n_tiles, P.out, P.out_len,
                                                                      P.out_cap, P.chunk_off, Q.tiles_per_frame,
                                                                      (P.mb1 - P.mb0) * 6, P.frame_off, P.stage_cap_units);
         }
     }
-    return cudaGetLastError();
+    return le != cudaSuccess ? le : cudaGetLastError();
 }
 
 }  // namespace awi

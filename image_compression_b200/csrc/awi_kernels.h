@@ -30,6 +30,31 @@ __device__ __forceinline__ int unscan_rt(int k) { return d_unscan[k]; }
 __device__ __forceinline__ int scan_rt(int i) { return d_scan[i]; }
 __device__ __forceinline__ uint32_t cos_bits_rt(int i) { return d_cos_bits[i]; }
 
+// ---- programmatic dependent launch.  Every kernel of this library starts with pdl_wait() (the grid in front of it in
+// the stream has completed and its writes are visible) followed by pdl_trigger() (the grid behind it may be placed
+// on the SMs now and park at its own pdl_wait()), and is launched through launch_pdl(): launch latency and the
+// ramp-down of one grid overlap the ramp-up of the next, which is most of what a short encode or decode step costs
+// beyond its kernels.  GPU_CODEC_NO_PDL=1 (measurement knob) launches them the ordinary way.
+#if defined(__CUDACC__)
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+bool pdl_enabled();
+template <class... KArgs, class... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), unsigned grid, unsigned block, size_t smem, cudaStream_t stream, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(block);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+#endif
+
 // ---- encode
 struct EncParams {
     const uint8_t* rows;          // address of bottom-up row 0 of the FULL image (may lie outside the
