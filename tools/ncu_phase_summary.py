@@ -35,12 +35,14 @@ def marks(lines, pats):
     return res
 
 
-M_ENC = marks(enc, [("top", "#include"), ("lookback helpers", "Look-back descriptors"), ("loader fn", "phase A"), ("colour rows", "phase B helpers"),
-                    ("sample_of", "sample (row y"), ("prologue", "the kernel"), ("A stage", "---- A:"), ("B setup+loop", "---- B:"),
-                    ("halo", "halo macroblock: only"), ("C exact", "---- C:"), ("D rle", "---- D:"), ("E scan", "---- E:"),
-                    ("lookback", "warp 0: decoupled"), ("compaction", "meanwhile / afterwards"), ("F copy", "---- F:"), ("launch", "-- launch")])
+M_ENC = marks(enc, [("top", "#include"), ("lookback helpers", "Look-back descriptors"), ("loader fn", "phase A"), ("colour helpers", "phase B helpers"),
+                    ("luma_piece", "uint4 luma_piece("), ("chroma_piece", "uint4 chroma_piece("), ("halo colour", "one colour-difference sample (halo"),
+                    ("sample addressing", "Sample bytes of a tile"), ("prologue", "the kernel"), ("A stage", "---- A:"), ("B1 colour loop", "---- B1:"),
+                    ("B2 dct/quant loop", "---- B2:"), ("halo", "halo macroblock: only"), ("C exact", "---- C:"), ("D rle", "---- D:"),
+                    ("E scan", "---- E:"), ("two-pass tail", "if (two_pass) {"), ("lookback", "---- single-pass tail"), ("F copy", "---- F:"),
+                    ("gather kernels", "two-pass mode, passes 2 and 3"), ("launch", "-- launch")])
 M_MTH = marks(mth, [("bit helpers", "bit helpers"), ("colour fwd", "forward colour"), ("colour inv", "inverse colour"), ("centred", "sample (0..255)"),
-                    ("aan", "forward DCT, fast path"), ("dc/quant_int", "Quantised DC from"), ("quant_flag", "Quantise one AAN-scaled"),
+                    ("aan", "forward DCT, fast path"), ("dc/quant_int", "Quantised DC from"), ("quant", "Quantise one AAN-scaled"),
                     ("fdct_quant_pack", "Fast DCT + quantise"), ("exact path", "forward DCT, exact path"), ("rle", "RLE of one chunk")])
 
 
