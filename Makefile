@@ -8,11 +8,11 @@ NVCCFLAGS := -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 --fmad=false 
 CSRC      := image_compression_b200/csrc
 LIB       := image_compression_b200/libgpu_codec.so
 OBJS      := $(CSRC)/awi_encode.o $(CSRC)/awi_decode.o $(CSRC)/gpu_codec.o
-HDRS      := $(CSRC)/codec_math.cuh $(CSRC)/codec_tables.h $(CSRC)/awi_kernels.h include/gpu_codec.h
+HDRS      := $(CSRC)/codec_math.cuh $(CSRC)/codec_tables.h $(CSRC)/colour_fix_tables.h $(CSRC)/awi_kernels.h include/gpu_codec.h
 
 all: $(LIB) host
 
-$(CSRC)/codec_tables.h: tools/gen_tables.py
+$(CSRC)/codec_tables.h $(CSRC)/colour_fix_tables.h: tools/gen_tables.py
 	python tools/gen_tables.py
 
 $(CSRC)/%.o: $(CSRC)/%.cu $(HDRS)

@@ -9,7 +9,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libgpu_codec.so")
 SOURCES = ["awi_encode.cu", "awi_decode.cu", "gpu_codec.cu"]
-HEADERS = ["codec_math.cuh", "codec_tables.h", "awi_kernels.h", os.path.join("..", "..", "include", "gpu_codec.h")]
+HEADERS = ["codec_math.cuh", "codec_tables.h", "colour_fix_tables.h", "awi_kernels.h", os.path.join("..", "..", "include", "gpu_codec.h")]
 # --fmad=false: the reference's arithmetic is "no FMA contraction" (SURVEY.md §0 fact 1);
 # the fast paths call fmaf explicitly where a fused operation is wanted.
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "--fmad=false", "-std=c++17",

@@ -34,6 +34,7 @@
 #include <stdlib.h>
 #include "codec_math.cuh"
 #include "awi_kernels.h"
+#include "colour_fix_tables.h"
 #include <mutex>
 #include <type_traits>
 
@@ -153,10 +154,17 @@ __device__ __forceinline__ uint4 load_piece(const uint8_t* src, int valid, int a
 // ---------------------------------------------------------------- phase B helpers
 __device__ __forceinline__ int byte_of(uint32_t w, int i) { return (int) ((w >> (8 * i)) & 0xffu); }
 
-// The literal fp64 expressions (color.c:31-33) are needed for roughly one pixel in a
-// thousand.  Kept out of line so the hot loop stays small.
-__device__ __noinline__ int luma_exact_call(int r, int g, int b) { return y_exact(r, g, b); }
-__device__ __noinline__ int chroma_exact_call(int r, int g, int b, int cr) { return cr ? cr_exact(r, g, b) : cb_exact(r, g, b); }
+// Where the rational quotient is not the reference's result (color.c:31-33 in fp64 lands just under an integer that
+// the exact value reaches: only when the numerator is an exact multiple of the denominator) one bit per (r, g) says so,
+// see colour_fix_tables.h.  A load from an 8 KB table instead of a detour through the fp64 pipe, which on this part
+// kept a warp busy for hundreds of cycles while its CTA waited at the next barrier (one sample in a thousand is a
+// multiple, so two warps in five met one in every pass).  Cb never needs a correction.
+static __device__ const uint32_t d_y_fix[2048] = AWI_Y_FIX_BITS;
+static __device__ const uint32_t d_cr_fix[2048] = AWI_CR_FIX_BITS;
+__device__ __forceinline__ uint32_t fix_bit(const uint32_t* table, uint32_t r, uint32_t g) {
+    const uint32_t i = (r << 8) | g;
+    return (__ldg(table + (i >> 5)) >> (i & 31u)) & 1u;
+}
 
 // dp2a: c + a.lo16 * b.byte[sel] + a.hi16 * b.byte[sel+1], sel = 0 (lo) or 2 (hi); the pixel bytes
 // are consumed straight from the packed words, no byte extraction.
@@ -220,10 +228,8 @@ __device__ __forceinline__ uint4 luma_piece(const uint32_t* w) {
 #pragma unroll
         for (int p = 0; p < 16; p++) {
             if (n[p] * 4294968u < 2000000u) {
-                int b = byte_of(w[(3 * p) >> 2], (3 * p) & 3);
-                int g = byte_of(w[(3 * p + 1) >> 2], (3 * p + 1) & 3);
-                int r = byte_of(w[(3 * p + 2) >> 2], (3 * p + 2) & 3);
-                f[p] = (uint32_t) luma_exact_call(r, g, b);
+                const uint32_t g = (uint32_t) byte_of(w[(3 * p + 1) >> 2], (3 * p + 1) & 3), r = (uint32_t) byte_of(w[(3 * p + 2) >> 2], (3 * p + 2) & 3);
+                f[p] -= fix_bit(d_y_fix, r, g);
             }
         }
     }
@@ -245,19 +251,15 @@ __device__ __forceinline__ uint4 chroma_piece(const uint32_t* w) {
         nb[x + 1] = (uint32_t) dp2a_lo_s(R_CB, w[wb + 1], dp2a_hi_s(BG_CB, w[wb], 1280000));
         nr[x + 1] = (uint32_t) dp2a_lo_s(R_CR, w[wb + 1], dp2a_hi_s(BG_CR, w[wb], 1280000));
     }
-    uint32_t fb[8], fr[8], least = 0xffffffffu;
+    uint32_t fb[8], fr[8], least = 0xffffffffu, unused = 0u;
 #pragma unroll
-    for (int x = 0; x < 8; x++) { fb[x] = div10000_q(nb[x], least); fr[x] = div10000_q(nr[x], least); }
-    if (least < 417800u) {
+    for (int x = 0; x < 8; x++) { fb[x] = div10000_q(nb[x], unused); fr[x] = div10000_q(nr[x], least); }
+    if (least < 417800u) {                           // (Cb's quotient is always the reference's result: no test)
 #pragma unroll
         for (int x = 0; x < 8; x++) {
-            const bool mb_ = nb[x] - fb[x] * 10000u == 0u, mr_ = nr[x] - fr[x] * 10000u == 0u;
-            if (mb_ || mr_) {
-                int b = byte_of(w[(6 * x) >> 2], (6 * x) & 3);
-                int g = byte_of(w[(6 * x + 1) >> 2], (6 * x + 1) & 3);
-                int r = byte_of(w[(6 * x + 2) >> 2], (6 * x + 2) & 3);
-                if (mb_) fb[x] = (uint32_t) chroma_exact_call(r, g, b, 0);
-                if (mr_) fr[x] = (uint32_t) chroma_exact_call(r, g, b, 1);
+            if (nr[x] - fr[x] * 10000u == 0u) {
+                const uint32_t g = (uint32_t) byte_of(w[(6 * x + 1) >> 2], (6 * x + 1) & 3), r = (uint32_t) byte_of(w[(6 * x + 2) >> 2], (6 * x + 2) & 3);
+                fr[x] -= fix_bit(d_cr_fix, r, g);
             }
         }
     }
@@ -265,12 +267,18 @@ __device__ __forceinline__ uint4 chroma_piece(const uint32_t* w) {
                       pack4(fr[0], fr[1], fr[2], fr[3]), pack4(fr[4], fr[5], fr[6], fr[7]));
 }
 
-// one colour-difference sample (halo macroblock sums); cr selects the coefficient set
-__device__ __forceinline__ int chroma_of(int r, int g, int b, bool cr) {
-    int kr = cr ? 5000 : -1687, kg = cr ? -4187 : -3313, kb = cr ? -813 : 5000;
-    uint32_t n = (uint32_t) (kr * r + kg * g + kb * b + 1280000);
+// single samples (halo macroblock sums)
+__device__ __forceinline__ int luma_px(int r, int g, int b) {
+    const uint32_t n = (uint32_t) (299 * r + 587 * g + 114 * b);
+    uint32_t q = __umulhi(n, 4294968u);
+    if (n - q * 1000u == 0u) q -= fix_bit(d_y_fix, (uint32_t) r, (uint32_t) g);
+    return (int) q;
+}
+__device__ __forceinline__ int chroma_px(int r, int g, int b, bool cr) {
+    const int kr = cr ? 5000 : -1687, kg = cr ? -4187 : -3313, kb = cr ? -813 : 5000;
+    const uint32_t n = (uint32_t) (kr * r + kg * g + kb * b + 1280000);
     uint32_t q = __umulhi(n, 3435974u) >> 3;
-    if (n - q * 10000u == 0u) return chroma_exact_call(r, g, b, cr ? 1 : 0);
+    if (cr && n - q * 10000u == 0u) q -= fix_bit(d_cr_fix, (uint32_t) r, (uint32_t) g);
     return (int) q;
 }
 
@@ -547,7 +555,7 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
             if (item < 128) {
                 int p = 2 * item, py = p >> 4, px = p & 15;
                 const uint8_t* q = S.halo + py * 48 + px * 3;
-                int s = luma_of(q[2], q[1], q[0]) + luma_of(q[5], q[4], q[3]);
+                int s = luma_px(q[2], q[1], q[0]) + luma_px(q[5], q[4], q[3]);
                 s += __shfl_xor_sync(0xffffffffu, s, 1);
                 s += __shfl_xor_sync(0xffffffffu, s, 2);
                 s += __shfl_xor_sync(0xffffffffu, s, 8);
@@ -556,7 +564,7 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
             } else {
                 int t = item - 128, yy = t >> 3, xx = t & 7;
                 const uint8_t* q = S.halo + 2 * yy * 48 + 6 * xx;
-                int cb = chroma_of(q[2], q[1], q[0], false), cr = chroma_of(q[2], q[1], q[0], true);
+                int cb = chroma_px(q[2], q[1], q[0], false), cr = chroma_px(q[2], q[1], q[0], true);
 #pragma unroll
                 for (int o = 16; o > 0; o >>= 1) {
                     cb += __shfl_xor_sync(0xffffffffu, cb, o);

@@ -132,3 +132,35 @@ def test_generated_tables_match_oracle(emul, port):
     bits = np.empty(64, np.uint32)
     emul.emul_cos_bits(bits.ctypes.data_as(C.POINTER(C.c_uint32)))
     assert (bits == port.cos_table().view(np.uint32).ravel()).all()
+
+
+def test_colour_fix_tables_reproduce_the_reference_on_every_colour(port):
+    """csrc/colour_fix_tables.h (generated): integer quotient minus the table bit == the reference's fp64 result
+    (color.c:31-33 + utils.c:10-17) for all 2^24 (r, g, b), which is what the encode kernel's colour phase computes;
+    Cb is the plain quotient."""
+    import os
+    import re
+    ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    path = os.path.join(ROOT, "image_compression_b200", "csrc", "colour_fix_tables.h")
+    text = open(path).read().replace("\\\n", " ")
+    tabs = {}
+    for name in ("Y", "CR"):
+        body = re.search(r"#define AWI_%s_FIX_BITS \{(.*?)\}" % name, text, re.S).group(1)
+        tabs[name] = np.array([int(x, 16) for x in re.findall(r"0x([0-9a-f]{8})u", body)], np.uint32)
+        assert tabs[name].size == 2048
+    for r0 in range(0, 256, 32):                       # 2^21 colours at a time
+        r, g, b = np.meshgrid(np.arange(r0, r0 + 32, dtype=np.int64), np.arange(256, dtype=np.int64), np.arange(256, dtype=np.int64), indexing="ij")
+        rgb = np.stack([r, g, b], axis=-1).reshape(-1, 3).astype(np.uint8)
+        want = port.rgb2ycc(rgb).astype(np.int64)
+        r, g, b = (rgb[:, i].astype(np.int64) for i in range(3))
+        idx = (r << 8) | g
+
+        def bit(t):
+            return (t[idx >> 5].astype(np.int64) >> (idx & 31)) & 1
+
+        ny = 299 * r + 587 * g + 114 * b
+        y = ny // 1000 - np.where(ny % 1000 == 0, bit(tabs["Y"]), 0)
+        ncb = -1687 * r - 3313 * g + 5000 * b + 1280000
+        ncr = 5000 * r - 4187 * g - 813 * b + 1280000
+        cr = ncr // 10000 - np.where(ncr % 10000 == 0, bit(tabs["CR"]), 0)
+        assert (y == want[:, 0]).all() and (ncb // 10000 == want[:, 1]).all() and (cr == want[:, 2]).all()

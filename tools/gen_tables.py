@@ -89,6 +89,61 @@ def error_bounds():
     return E, a
 
 
+def colour_fix_tables():
+    """Where the reference's fp64 colour sums land below an integer that the exact rational reaches.
+
+    color.c:31-33 evaluates Y = 0.299 r + 0.587 g + 0.114 b (and Cb, Cr likewise, + 128) left to right in fp64 and
+    truncates.  The rational value is n / 1000 (n / 10000) with an integer numerator n, so floor(n / 1000) is the
+    reference's result unless n is an exact multiple: then fp64 may end one ulp below the integer and truncation gives
+    one less.  For a given (r, g) at most one b makes the Y (or Cr) numerator a multiple, so one bit per (r, g) says
+    whether that happens: 65536 bits per table, bit index (r << 8) | g.  Cb never differs (checked here).
+    numpy's float64 arithmetic is IEEE, one rounding per operation, no contraction: the reference's -O0 build."""
+    r, g, b = np.meshgrid(np.arange(256, dtype=np.int64), np.arange(256, dtype=np.int64), np.arange(256, dtype=np.int64), indexing="ij")
+    rf, gf, bf = r.astype(np.float64), g.astype(np.float64), b.astype(np.float64)
+
+    def clamp_trunc(v):
+        return np.clip(np.trunc(v), 0, 255).astype(np.int64)
+
+    tabs = {}
+    specs = {
+        "Y": (299 * r + 587 * g + 114 * b, 1000, clamp_trunc((0.299 * rf + 0.587 * gf) + 0.114 * bf)),
+        "CB": (-1687 * r - 3313 * g + 5000 * b + 1280000, 10000, clamp_trunc(((-0.1687 * rf - 0.3313 * gf) + 0.5 * bf) + 128.0)),
+        "CR": (5000 * r - 4187 * g - 813 * b + 1280000, 10000, clamp_trunc(((0.5 * rf - 0.4187 * gf) - 0.0813 * bf) + 128.0)),
+    }
+    for name, (n, den, ref) in specs.items():
+        q = n // den
+        diff = q - ref
+        assert ((diff == 0) | ((diff == 1) & (n % den == 0))).all(), name      # only exact multiples differ, and by one
+        bits = (diff == 1)
+        assert (bits.sum(axis=2) <= 1).all()
+        if name == "CB":
+            assert not bits.any()                                           # Cb needs no table
+            continue
+        flat = bits.any(axis=2).reshape(-1)                                  # index (r << 8) | g
+        words = np.zeros(2048, np.uint32)
+        idx = np.nonzero(flat)[0]
+        np.bitwise_or.at(words, idx >> 5, (np.uint32(1) << (idx & 31).astype(np.uint32)))
+        tabs[name] = (words, int(bits.sum()))
+    return tabs
+
+
+def write_colour_fix(path):
+    tabs = colour_fix_tables()
+    out = ["// GENERATED by tools/gen_tables.py — do not edit.",
+           "// Exact-multiple corrections of the forward colour transform (color.c:31-33): bit (r << 8 | g) of the table is set",
+           "// when the one b that makes the numerator an exact multiple of the denominator gives a reference result one below",
+           "// the rational quotient (fp64 lands just under the integer).  Cb has no such case.",
+           "#pragma once", "#include <stdint.h>"]
+    for name, (words, cnt) in tabs.items():
+        out.append("// %d of 2^24 colours" % cnt)
+        out.append("#define AWI_%s_FIX_BITS { \\" % name)
+        for i in range(0, 2048, 16):
+            out.append("    " + ", ".join("0x%08xu" % w for w in words[i:i + 16]) + (", \\" if i + 16 < 2048 else " }"))
+    with open(path, "w") as f:
+        f.write("\n".join(out) + "\n")
+    print("wrote", os.path.normpath(path))
+
+
 def f32(x):
     return float(np.float32(x))
 
@@ -141,6 +196,7 @@ def main():
     with open(path, "w") as f:
         f.write("\n".join(out) + "\n")
     print("wrote", os.path.normpath(path))
+    write_colour_fix(os.path.join(os.path.dirname(path), "colour_fix_tables.h"))
 
 
 if __name__ == "__main__":
