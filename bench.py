@@ -252,9 +252,9 @@ def run_reference_arm(args) -> dict:
 
 def enc_launches(n_mb: int, frames: int = 1) -> int:
     """Kernels one device-resident encode call launches: awi_encode_kernel + the fused scan/gather pass up to
-    4096 tiles of 32 macroblocks, otherwise + enc_scan_tiles + enc_gather_tiles (awi_encode.cu launch_encode)."""
+    65536 tiles of 32 macroblocks, otherwise + enc_scan_tiles + enc_gather_tiles (awi_encode.cu launch_encode)."""
     tiles = (n_mb + 31) // 32 * frames
-    return 2 if tiles <= 4096 else 3
+    return 2 if tiles <= 65536 else 3
 
 
 def dec_launches(payload_bytes: int, n_mb: int) -> int:
@@ -444,7 +444,7 @@ def run_encode(args, E: Env) -> dict | None:
     achieved = alg_bytes / (step_ms * 1e-3) / 1e9
     traffic, traffic_src = traffic_from_profile(f"{args.workload}_{args.kind}")
     n_tiles = (mbw * mbh + 31) // 32 * frames
-    kernels = ("awi_encode_kernel + enc_scan_gather_tiles" if (n_tiles if not striped else n_tiles // E.world) <= 4096
+    kernels = ("awi_encode_kernel + enc_scan_gather_tiles" if (n_tiles if not striped else n_tiles // E.world) <= 65536
                else "awi_encode_kernel + enc_scan_tiles + enc_gather_tiles")
     roofline = {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak * E.world, "unit": "GB/s",
                 "frac": round(achieved / (peak * E.world), 4), "traffic": traffic, "traffic_source": traffic_src,

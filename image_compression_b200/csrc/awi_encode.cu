@@ -221,15 +221,21 @@ __device__ __forceinline__ uint4 luma_piece(const uint32_t* w) {
         n[4 * q] = luma_num<0>(x[0], x[0]); n[4 * q + 1] = luma_num<3>(x[0], x[1]);
         n[4 * q + 2] = luma_num<2>(x[1], x[2]); n[4 * q + 3] = luma_num<1>(x[2], x[2]);
     }
-    uint32_t f[16], least = 0xffffffffu;
+    // the multiple test is kept per group of four samples, so that a lane that has one looks at four samples, not sixteen
+    uint32_t f[16], least[4] = { 0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu };
 #pragma unroll
-    for (int p = 0; p < 16; p++) f[p] = div1000_q(n[p], least);
-    if (least < 2000000u) {                          // an exact multiple of 1000 somewhere in the piece (grey pixels are)
+    for (int p = 0; p < 16; p++) f[p] = div1000_q(n[p], least[p >> 2]);
+    if (min(min(least[0], least[1]), min(least[2], least[3])) < 2000000u) {      // an exact multiple of 1000 somewhere in the piece (grey pixels are)
 #pragma unroll
-        for (int p = 0; p < 16; p++) {
-            if (n[p] * 4294968u < 2000000u) {
-                const uint32_t g = (uint32_t) byte_of(w[(3 * p + 1) >> 2], (3 * p + 1) & 3), r = (uint32_t) byte_of(w[(3 * p + 2) >> 2], (3 * p + 2) & 3);
-                f[p] -= fix_bit(d_y_fix, r, g);
+        for (int q = 0; q < 4; q++) {
+            if (least[q] < 2000000u) {
+#pragma unroll
+                for (int p = 4 * q; p < 4 * q + 4; p++) {
+                    if (n[p] * 4294968u < 2000000u) {
+                        const uint32_t g = (uint32_t) byte_of(w[(3 * p + 1) >> 2], (3 * p + 1) & 3), r = (uint32_t) byte_of(w[(3 * p + 2) >> 2], (3 * p + 2) & 3);
+                        f[p] -= fix_bit(d_y_fix, r, g);
+                    }
+                }
             }
         }
     }
@@ -678,6 +684,7 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
             const unsigned at = atomicAdd(P.stage_cursor, units);
             S.tile_base = at;
             P.tile_info[tile] = make_uint2(at, total);
+            if (P.bucket != nullptr) atomicAdd(P.bucket + (tile >> 6), total);      // the gather pass adds up 64 tiles at a time
             if ((unsigned long long) at + units > P.stage_cap_units) atomicOr(P.err, 1u);
         }
         if (compact_ok) {
@@ -898,14 +905,21 @@ __global__ void __launch_bounds__(256) enc_scan_gather_tiles(const uint8_t* __re
                                                              unsigned int* __restrict__ stage_cursor,
                                                              uint32_t* __restrict__ chunk_off, int tiles_per_frame,
                                                              int chunks_per_frame, unsigned long long* __restrict__ frame_off,
-                                                             unsigned long long stage_cap_units) {
+                                                             unsigned long long stage_cap_units,
+                                                             unsigned int* __restrict__ bucket, unsigned int* __restrict__ gather_done) {
     __shared__ unsigned long long wsum[8];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     pdl_wait();                       // every tile of the encode kernel is staged and recorded
     pdl_trigger();
     const int first = blockIdx.x * 8;
     unsigned long long mine = 0;
-    for (int t = tid; t < first; t += 256) mine += tile_info[t].y;
+    if (bucket != nullptr) {          // larger frames: the encode kernel has added the byte counts up per 64 tiles
+        const int b = first >> 6;
+        for (int t = tid; t < b; t += 256) mine += bucket[t];
+        for (int t = (b << 6) + tid; t < first; t += 256) mine += tile_info[t].y;
+    } else {
+        for (int t = tid; t < first; t += 256) mine += tile_info[t].y;
+    }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) mine += __shfl_xor_sync(0xffffffffu, mine, o);
     if (lane == 0) wsum[warp] = mine;
@@ -922,6 +936,13 @@ __global__ void __launch_bounds__(256) enc_scan_gather_tiles(const uint8_t* __re
 #pragma unroll
     for (int w = 0; w < 8; w++) off += wsum[w];
     off += before;
+    if (bucket != nullptr && tid == 0) {                      // the CTA that reads the sums last leaves them at zero for the next launch
+        __threadfence();
+        if (atomicAdd(gather_done, 1u) == gridDim.x - 1) {
+            for (int t = 0; t < (n_tiles + 63) >> 6; t++) bucket[t] = 0u;
+            *gather_done = 0u;
+        }
+    }
     if (tile >= n_tiles) return;
     const bool fits = off + total <= out_cap;
     if (tile == n_tiles - 1 && lane == 0) {                  // the end of the last tile is the end of the payload
@@ -988,14 +1009,16 @@ cudaError_t launch_encode(const EncParams& P, int n_tiles, cudaStream_t stream) 
     Q.n_tiles = n_tiles;
     if (Q.compact_cap <= 0 || Q.compact_cap > COMPACT_CAP) Q.compact_cap = COMPACT_CAP;
     if (Q.tiles_per_frame <= 0) { Q.tiles_per_frame = n_tiles; Q.frame_stride = 0; }      // a single frame
+    if (n_tiles <= ENC_FUSED_MAX_TILES || n_tiles > 64 * ENC_BUCKETS) Q.bucket = nullptr;   // (the kernel adds into them only where the gather pass reads them)
     cudaError_t le = launch_pdl(awi_encode_kernel, (unsigned) n_tiles, THREADS, sizeof(EncSmem), stream, Q);
     if (le != cudaSuccess) return le;
     if (P.stage != nullptr) {
-        if (n_tiles <= ENC_FUSED_MAX_TILES) {
+        const bool buckets = n_tiles > ENC_FUSED_MAX_TILES && P.bucket != nullptr && n_tiles <= 64 * ENC_BUCKETS;
+        if (n_tiles <= ENC_FUSED_MAX_TILES || buckets) {
             le = launch_pdl(enc_scan_gather_tiles, (unsigned) (n_tiles + 7) / 8, 256, 0, stream, P.stage, P.tile_info, n_tiles, P.out, P.out_len, P.out_len_user,
                                                                          P.chain_in, P.chain_out, P.out_cap, P.err, P.stage_cursor,
                                                                          P.chunk_off, Q.tiles_per_frame, (P.mb1 - P.mb0) * 6, P.frame_off,
-                                                                         P.stage_cap_units);
+                                                                         P.stage_cap_units, buckets ? P.bucket : (unsigned int*) nullptr, P.gather_done);
         } else {
             le = launch_pdl(enc_scan_tiles, 1, 1024, 0, stream, P.tile_info, n_tiles, P.tile_off, P.out_len, P.chain_in, P.chain_out, P.out_cap, P.err,
                                                    P.out_len_user, P.stage_cursor);

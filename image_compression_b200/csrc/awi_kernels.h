@@ -82,6 +82,8 @@ struct EncParams {
     uint8_t* stage;               // 16-byte aligned
     unsigned long long stage_cap_units;   // capacity in 16-byte units
     unsigned int* stage_cursor;   // zero before the first launch; enc_scan_tiles leaves it at zero again
+    unsigned int* bucket;         // optional, ENC_BUCKETS words, zero before the first launch: byte counts per 64 tiles (left at zero again)
+    unsigned int* gather_done;    // with `bucket`: one word, zero before the first launch
     uint2* tile_info;             // per tile: (staging offset in units, bytes)
     unsigned long long* tile_off; // per tile: payload offset
     const unsigned long long* chain_in;   // optional: payload offset to start at (sub-stripes of one frame, groups of a batch)
@@ -90,6 +92,7 @@ struct EncParams {
     uint32_t* chunk_off;          // optional: byte offset of every chunk in `out`
     int8_t* qcoef;                // optional: quantised coefficients, 64 per chunk, scan order
 };
+constexpr int ENC_BUCKETS = 1024;             // frames of up to 64 * ENC_BUCKETS tiles scan and gather in one kernel
 size_t enc_smem_bytes();
 cudaError_t launch_encode(const EncParams& P, int n_tiles, cudaStream_t stream);
 

@@ -48,7 +48,8 @@ constexpr int MAX_SUB = 32;               // sub-stripes a frame is cut into to 
 constexpr size_t SUB_BYTES = 48u << 20;   // aim for ~48 MB of pixels per sub-stripe
 constexpr size_t SUB_BYTES_MIN = 4u << 20;
 constexpr int RING_SLOTS = 3;              // page-locked staging slots per context for uploads from pageable memory
-constexpr size_t ENC_WS_HEADER = 256;     // [0,8) payload length, [8,12) tile ticket, [16,20) staging cursor
+constexpr size_t ENC_WS_HEADER = 256 + 4 * awi::ENC_BUCKETS;   // [0,8) payload length, [8,12) tile ticket, [16,20) staging cursor, [24,28) gather count,
+                                                             // [256, ...) byte counts per 64 tiles
 
 struct Buf {
     uint8_t* p = nullptr;
@@ -448,6 +449,8 @@ bool encode_dev_impl(Ctx* c, const uint8_t* d_rows, int width, int height, long 
     P.stage = c->enc_stage.p;
     P.stage_cap_units = (stage_bytes - 256) / 16;
     P.stage_cursor = reinterpret_cast<unsigned int*>(c->enc_ws.p + 16);
+    P.gather_done = reinterpret_cast<unsigned int*>(c->enc_ws.p + 24);
+    P.bucket = reinterpret_cast<unsigned int*>(c->enc_ws.p + 256);
     P.tile_info = reinterpret_cast<uint2*>(c->enc_ws.p + ENC_WS_HEADER);
     P.tile_off = reinterpret_cast<unsigned long long*>(c->enc_ws.p + ENC_WS_HEADER + (size_t) n_tiles * 8);
     P.chain_in = d_chain ? d_chain + (chain_slot & 1) : nullptr;
