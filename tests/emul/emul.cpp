@@ -58,6 +58,51 @@ void emul_fast_only(const uint8_t* px, int chroma, int* chunk, uint64_t* amb_out
     *amb_out = amb;
 }
 
+// AAN outputs of the fast path (before the quantiser; scaled by 8 a_u a_v relative to the reference's value) next to
+// the reference's exact pre-truncation value ((0.25 cu cv) * sum, dct.c:50) for every position: the test compares
+// their distance with the a-priori bound AWI_EPS_T the ambiguity thresholds are built from.
+void emul_fast_vs_exact(const uint8_t* px, double* fast_scaled, double* exact_t) {
+    float d[64];
+    for (int i = 0; i < 64; i++) d[i] = centred(px[i]);
+    for (int y = 0; y < 8; y++)
+        aan8(d[8 * y + 0], d[8 * y + 1], d[8 * y + 2], d[8 * y + 3], d[8 * y + 4], d[8 * y + 5], d[8 * y + 6], d[8 * y + 7]);
+    for (int x = 0; x < 8; x++)
+        aan8(d[x], d[8 + x], d[16 + x], d[24 + x], d[32 + x], d[40 + x], d[48 + x], d[56 + x]);
+    for (int k = 0; k < 64; k++) {
+        int u = k >> 3, v = k & 7;
+        double sum = 0.0;
+        for (int y = 0; y < 8; y++)
+            for (int x = 0; x < 8; x++)
+                sum += (double) exact_product((int) px[y * 8 + x] - 128, cosf_tab(y, u), cosf_tab(x, v));
+        fast_scaled[k] = (double) d[k];
+        exact_t[k] = dmul_rn(fdct_scale(u, v), sum);
+    }
+}
+
+// The encode kernel's own flag expression (awi_encode.cu phase B2): ONE threshold for every position, the tightest of
+// the table (AWI_GT_MIN_*), compared with |g - rn(g)| of each coefficient; the DC position is never flagged.
+// Returns the fast-path chunk and the flag mask (natural positions).
+void emul_fast_kernel_flags(const uint8_t* px, int chroma, int* chunk, uint64_t* amb_out) {
+    float d[64];
+    for (int i = 0; i < 64; i++) d[i] = centred(px[i]);
+    for (int y = 0; y < 8; y++)
+        aan8(d[8 * y + 0], d[8 * y + 1], d[8 * y + 2], d[8 * y + 3], d[8 * y + 4], d[8 * y + 5], d[8 * y + 6], d[8 * y + 7]);
+    for (int x = 0; x < 8; x++)
+        aan8(d[x], d[8 + x], d[16 + x], d[24 + x], d[32 + x], d[40 + x], d[48 + x], d[56 + x]);
+    const float gt = chroma ? AWI_GT_MIN_CHROMA : AWI_GT_MIN_LUMA;
+    uint64_t amb = 0;
+    int q[64];
+    for (int k = 1; k < 64; k++) {
+        float t;
+        const float dist = quant_absdiff(d[k], chroma ? gk_chroma(k) : gk_luma(k), chroma ? gc_chroma(k) : gc_luma(k), t);
+        if (dist > gt) amb |= 1ull << k;
+        q[k] = (int) (int8_t) (f2u(t) & 0xffu);
+    }
+    q[0] = quant_int(dc_coef_from_sum((int) d[0]), chroma ? 17 : 16);
+    for (int i = 0; i < 64; i++) chunk[i] = q[scan_tab(i)];
+    *amb_out = amb;
+}
+
 int emul_rle(const int* chunk, int prev_dc, uint8_t* out) {
     uint64_t nz = 0;
     for (int i = 1; i < 64; i++) if (chunk[i]) nz |= 1ull << i;

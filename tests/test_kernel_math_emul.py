@@ -164,3 +164,55 @@ def test_colour_fix_tables_reproduce_the_reference_on_every_colour(port):
         ncr = 5000 * r - 4187 * g - 813 * b + 1280000
         cr = ncr // 10000 - np.where(ncr % 10000 == 0, bit(tabs["CR"]), 0)
         assert (y == want[:, 0]).all() and (ncb // 10000 == want[:, 1]).all() and (cr == want[:, 2]).all()
+
+
+def _eps_t():
+    import os
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    text = open(os.path.join(root, "image_compression_b200", "csrc", "codec_tables.h")).read()
+    body = re.search(r"#define AWI_EPS_T \{(.*?)\}", text).group(1)
+    return np.array([float(x) for x in body.split(",")])
+
+
+def test_fast_path_stays_inside_the_a_priori_bound(emul):
+    """|fast AAN value - reference's exact pre-truncation value| <= AWI_EPS_T[k] at every position, on the blocks that
+    push each coefficient to its largest magnitude (sign patterns at full swing), on flat blocks and on noise.  The bound
+    is an a-priori worst case (tools/gen_tables.py: every rounding of the butterfly network at its largest possible
+    operand, second-order terms kept, plus the reference's own distance from the ideal DCT); the ambiguity thresholds are
+    built from 1.25 x it, so the measured maximum has to sit well below 1."""
+    eps = _eps_t()
+    a = np.array([1.0] + [np.sqrt(2) * np.cos(k * np.pi / 16) for k in range(1, 8)])
+    K = 1.0 / (8.0 * np.outer(a, a)).ravel()
+    rng = np.random.default_rng(21)
+    blocks = np.concatenate([_blocks_adversarial(), rng.integers(0, 256, (3000, 64)).astype(np.uint8),
+                             np.where(rng.integers(0, 2, (3000, 64)) > 0, 255, 0).astype(np.uint8)])
+    f64p = C.POINTER(C.c_double)
+    worst = np.zeros(64)
+    for b in blocks:
+        b = np.ascontiguousarray(b, np.uint8)
+        fast, exact = np.empty(64), np.empty(64)
+        emul.emul_fast_vs_exact(b.ctypes.data_as(u8p), fast.ctypes.data_as(f64p), exact.ctypes.data_as(f64p))
+        worst = np.maximum(worst, np.abs(fast * K - exact))
+    assert (worst <= eps).all(), (worst / eps).max()
+    assert (worst / eps).max() < 0.8            # the bound is a worst case over all roundings at once: nothing gets close
+
+
+def test_kernel_flag_expression_is_safe(emul, port):
+    """The encode kernel flags with ONE threshold (the tightest of the per-position table) and a running maximum; what it
+    does not flag must already equal the reference, and what it flags is a superset of the per-position flags."""
+    rng = np.random.default_rng(22)
+    from oracle import port as _p
+    _, _, scan = _p().tables()
+    blocks = np.concatenate([_blocks_adversarial(), rng.integers(0, 256, (2500, 64)).astype(np.uint8)])
+    for chroma in (0, 1):
+        for b in blocks:
+            b = np.ascontiguousarray(b, np.uint8)
+            chunk, chunk2 = np.empty(64, np.int32), np.empty(64, np.int32)
+            amb, amb2 = C.c_uint64(), C.c_uint64()
+            emul.emul_fast_kernel_flags(b.ctypes.data_as(u8p), chroma, chunk.ctypes.data_as(i32p), C.byref(amb))
+            emul.emul_fast_only(b.ctypes.data_as(u8p), chroma, chunk2.ctypes.data_as(i32p), C.byref(amb2))
+            assert (chunk == chunk2).all() and (amb2.value & ~amb.value) == 0
+            want = port.transform(b, chroma)
+            for i in np.nonzero(chunk != want)[0]:
+                assert (amb.value >> int(scan[i])) & 1, "unflagged fast-path mismatch under the kernel's flag expression"
