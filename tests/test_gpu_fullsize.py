@@ -141,3 +141,39 @@ def test_every_colour_through_the_encoder(gpu, port):
     p, _ = _encode(gpu, rows, w, h, stride)
     want = port.encode_bgr(rows.cpu().numpy(), w, h, stride)
     assert p.cpu().numpy().tobytes() == want.tobytes()
+
+
+def test_long_batch_takes_the_three_kernel_path(gpu, port):
+    """Above 65536 tiles the tile scan and the gather are kernels of their own again (enc_scan_tiles + enc_gather_tiles):
+    260 x 1080p frames (66 300 tiles, 1.6 GB of pixels) in one gpu_codec_encode_batch_bgr_dev call.  Every frame's payload must
+    equal what the same frame gives on its own (through the one-kernel gather), and the oracle's for a sample of them; a batch
+    of 200 frames (51 000 tiles: per-64-tile sums inside one kernel) is checked the same way."""
+    import torch
+    w, h = 1920, 1080
+    stride = 3 * w
+    fb = stride * h
+    n_max = 260
+    buf = torch.empty(n_max * fb, dtype=torch.uint8, device="cuda")
+    for f in range(n_max):
+        gpu.synth_dev(0, buf[f * fb:(f + 1) * fb], w, h, stride, KIND["photo" if f % 3 else "noise"], synth.SEED_BASE + 4, f)
+    cap = gpu.max_payload_bytes(w, h) + 16
+    single = torch.empty(cap, dtype=torch.uint8, device="cuda")
+    ln = torch.zeros(1, dtype=torch.int64, device="cuda")
+    ref_digest = {}
+    for f in (0, 1, 63, 64, 127, 199, 200, 258, 259):
+        gpu.encode_dev(0, buf[f * fb:(f + 1) * fb], w, h, stride, single, ln)
+        gpu.sync_check(0)
+        ref_digest[f] = single[: int(ln.item())].cpu().numpy().tobytes()
+    assert ref_digest[0] == port.encode_bgr(buf[:fb].cpu().numpy(), w, h, stride).tobytes()
+    assert ref_digest[259] == port.encode_bgr(buf[259 * fb:260 * fb].cpu().numpy(), w, h, stride).tobytes()
+    payload = torch.empty(n_max * 1200000, dtype=torch.uint8, device="cuda")     # photo frames take ~0.36 MB, noise ~2 MB: 235 MB in all
+    for n in (260, 200):
+        off = torch.zeros(n + 1, dtype=torch.int64, device="cuda")
+        for _ in range(2):                                                    # twice: the second call meets the first one's leftovers
+            gpu.encode_batch_dev(0, buf, n, fb, w, h, stride, payload, off)
+            gpu.sync_check(0)
+        o = off.cpu().numpy()
+        assert o[0] == 0 and (np.diff(o) > 0).all()
+        for f, want in ref_digest.items():
+            if f < n:
+                assert payload[o[f]:o[f + 1]].cpu().numpy().tobytes() == want, (n, f)
