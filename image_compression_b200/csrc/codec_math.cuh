@@ -112,11 +112,14 @@ AWI_HD int clamp_trunc(double v) {
     // utils.c:10-17: >255 -> 255, <0 -> 0, else truncate.  Truncation first is equivalent: values above 255
     // truncate to >= 255, values below 0 truncate to <= 0 (the conversion saturates far outside the int range).
 #if defined(__CUDA_ARCH__)
-    int i = __double2int_rz(v);
+    // one conversion: float -> integer conversions saturate to the destination range (u8: 0..255) and truncate with .rzi
+    unsigned int i;
+    asm("cvt.rzi.u8.f64 %0, %1;" : "=r"(i) : "d"(v));
+    return (int) i;
 #else
     int i = v >= 2147483647.0 ? 2147483647 : (v <= -2147483648.0 ? (-2147483647 - 1) : (int) v);
-#endif
     return i > 255 ? 255 : (i < 0 ? 0 : i);
+#endif
 }
 
 AWI_HD int y_exact(int r, int g, int b) {
