@@ -15,7 +15,7 @@
 //      f32x2 registers (FADD2/FMUL2/FFMA2): AAN row pass -> 8x8 transpose through smem -> AAN column pass ->
 //      quantise (+ambiguity flags) with per-lane constants -> scan-order int8 coefficients in smem;
 //      exact DC;  halo macroblock DCs.  One loop body serves luma and chroma pairs; the tile's 24
-//      iterations (8 blocks each) are dealt round-robin to the warps.
+//      iterations (8 blocks each): four warps take the luma pairs, two the chroma pairs.
 //   C  flagged coefficients recomputed warp-cooperatively in the reference's exact
 //      operation order
 //   D  one thread per chunk: run-length symbols + bit packing into a smem slot
@@ -161,9 +161,15 @@ __device__ __forceinline__ int byte_of(uint32_t w, int i) { return (int) ((w >> 
 // multiple, so two warps in five met one in every pass).  Cb never needs a correction.
 static __device__ const uint32_t d_y_fix[2048] = AWI_Y_FIX_BITS;
 static __device__ const uint32_t d_cr_fix[2048] = AWI_CR_FIX_BITS;
-__device__ __forceinline__ uint32_t fix_bit(const uint32_t* table, uint32_t r, uint32_t g) {
-    const uint32_t i = (r << 8) | g;
+__device__ __forceinline__ uint32_t fix_bit(const uint32_t* table, uint32_t i) {      // i = (r << 8) | g
     return (__ldg(table + (i >> 5)) >> (i & 31u)) & 1u;
+}
+// (r << 8) | g of the pixel whose B byte is byte `byte0` of the packed words w[] (a literal after unrolling):
+// one PRMT where G and R share a word
+__device__ __forceinline__ uint32_t rg_index(const uint32_t* w, int byte0) {
+    const int wg = (byte0 + 1) >> 2, bg = (byte0 + 1) & 3, wr = (byte0 + 2) >> 2, br = (byte0 + 2) & 3;
+    if (wg == wr) return __byte_perm(w[wg], 0u, (uint32_t) (bg | (br << 4) | 0x4400));
+    return __byte_perm(w[wg], w[wr], (uint32_t) (bg | ((4 + br) << 4))) & 0xffffu;
 }
 
 // dp2a: c + a.lo16 * b.byte[sel] + a.hi16 * b.byte[sel+1], sel = 0 (lo) or 2 (hi); the pixel bytes
@@ -222,20 +228,20 @@ __device__ __forceinline__ uint4 luma_piece(const uint32_t* w) {
         n[4 * q + 2] = luma_num<2>(x[1], x[2]); n[4 * q + 3] = luma_num<1>(x[2], x[2]);
     }
     // the multiple test is kept per group of four samples, so that a lane that has one looks at four samples, not sixteen
-    uint32_t f[16], least[4] = { 0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu };
+    // (measured: groups of 2 or 8 samples, one test per sample and warp votes around the slow path are all slower)
+    constexpr int G = 4, NG = 16 / G;
+    uint32_t f[16], least[NG];
 #pragma unroll
-    for (int p = 0; p < 16; p++) f[p] = div1000_q(n[p], least[p >> 2]);
-    if (min(min(least[0], least[1]), min(least[2], least[3])) < 2000000u) {      // an exact multiple of 1000 somewhere in the piece (grey pixels are)
+    for (int q = 0; q < NG; q++) least[q] = 0xffffffffu;
 #pragma unroll
-        for (int q = 0; q < 4; q++) {
-            if (least[q] < 2000000u) {
+    for (int p = 0; p < 16; p++) f[p] = div1000_q(n[p], least[p / G]);
+    // Slow path, one sample in a thousand: the table lookup.
 #pragma unroll
-                for (int p = 4 * q; p < 4 * q + 4; p++) {
-                    if (n[p] * 4294968u < 2000000u) {
-                        const uint32_t g = (uint32_t) byte_of(w[(3 * p + 1) >> 2], (3 * p + 1) & 3), r = (uint32_t) byte_of(w[(3 * p + 2) >> 2], (3 * p + 2) & 3);
-                        f[p] -= fix_bit(d_y_fix, r, g);
-                    }
-                }
+    for (int q = 0; q < NG; q++) {
+        if (least[q] < 2000000u) {                     // an exact multiple of 1000 in group q (grey pixels are)
+#pragma unroll
+            for (int p = G * q; p < G * q + G; p++) {
+                if (n[p] * 4294968u < 2000000u) f[p] -= fix_bit(d_y_fix, rg_index(w, 3 * p));
             }
         }
     }
@@ -263,10 +269,7 @@ __device__ __forceinline__ uint4 chroma_piece(const uint32_t* w) {
     if (least < 417800u) {                           // (Cb's quotient is always the reference's result: no test)
 #pragma unroll
         for (int x = 0; x < 8; x++) {
-            if (nr[x] - fr[x] * 10000u == 0u) {
-                const uint32_t g = (uint32_t) byte_of(w[(6 * x + 1) >> 2], (6 * x + 1) & 3), r = (uint32_t) byte_of(w[(6 * x + 2) >> 2], (6 * x + 2) & 3);
-                fr[x] -= fix_bit(d_cr_fix, r, g);
-            }
+            if (nr[x] - fr[x] * 10000u == 0u) fr[x] -= fix_bit(d_cr_fix, rg_index(w, 6 * x));
         }
     }
     return make_uint4(pack4(fb[0], fb[1], fb[2], fb[3]), pack4(fb[4], fb[5], fb[6], fb[7]),
@@ -277,14 +280,14 @@ __device__ __forceinline__ uint4 chroma_piece(const uint32_t* w) {
 __device__ __forceinline__ int luma_px(int r, int g, int b) {
     const uint32_t n = (uint32_t) (299 * r + 587 * g + 114 * b);
     uint32_t q = __umulhi(n, 4294968u);
-    if (n - q * 1000u == 0u) q -= fix_bit(d_y_fix, (uint32_t) r, (uint32_t) g);
+    if (n - q * 1000u == 0u) q -= fix_bit(d_y_fix, ((uint32_t) r << 8) | (uint32_t) g);
     return (int) q;
 }
 __device__ __forceinline__ int chroma_px(int r, int g, int b, bool cr) {
     const int kr = cr ? 5000 : -1687, kg = cr ? -4187 : -3313, kb = cr ? -813 : 5000;
     const uint32_t n = (uint32_t) (kr * r + kg * g + kb * b + 1280000);
     uint32_t q = __umulhi(n, 3435974u) >> 3;
-    if (cr && n - q * 10000u == 0u) q -= fix_bit(d_cr_fix, (uint32_t) r, (uint32_t) g);
+    if (cr && n - q * 10000u == 0u) q -= fix_bit(d_cr_fix, ((uint32_t) r << 8) | (uint32_t) g);
     return (int) q;
 }
 
@@ -344,7 +347,7 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
     if (tid < 6) S.halo_sum[tid] = 0;
     S.amb[tid] = 0;
     // batches: tiles_per_frame tiles per frame, frames frame_stride bytes apart, predictors restart per frame
-    const int frame = tile / P.tiles_per_frame, tile_in = tile - frame * P.tiles_per_frame;
+    const int frame = fast_div(tile, P.div_tpf), tile_in = tile - frame * P.tiles_per_frame;
     const int mb_first = P.mb0 + tile_in * TILE_MB;              // raster index inside the frame
     const int n_mb = min(TILE_MB, P.mb1 - mb_first);
     const bool has_halo = mb_first > 0;
@@ -356,7 +359,7 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
     //      16-byte piece column (macroblock m, piece k) x 8 rows, with edge handling.
     {
         const uint8_t* const rows = P.rows + (long long) frame * P.frame_stride;
-        const int my_first = mb_first / P.mbw, mx_first = mb_first - my_first * P.mbw;
+        const int my_first = fast_div(mb_first, P.div_mbw), mx_first = mb_first - my_first * P.mbw;
         // a full tile of whole macroblocks inside the image that spans at most two macroblock rows: every pixel row of
         // the tile is one contiguous run in the frame, or two where the tile wraps onto the next macroblock row
         const int n_a = min(TILE_MB, P.mbw - mx_first);          // macroblocks of the tile on its first macroblock row
@@ -384,7 +387,7 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
         for (int i = 0; i < 8; i++) v[i] = make_uint4(0, 0, 0, 0);
         if (!bulk && m < n_mb) {
             const int g = mb_first + m;
-            const int my = g / P.mbw, mx = g - my * P.mbw;
+            const int my = fast_div(g, P.div_mbw), mx = g - my * P.mbw;
             const int xb = mx * 48 + k * 16;
             const int valid = P.width * 3 - xb;
             const int y0 = my * 16 + r0;
@@ -402,7 +405,7 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
         uint4 h = make_uint4(0, 0, 0, 0);
         if (tid < 48 && has_halo) {
             const int g = mb_first - 1, row = tid / 3, kk = tid - 3 * row;
-            const int my = g / P.mbw, mx = g - my * P.mbw;
+            const int my = fast_div(g, P.div_mbw), mx = g - my * P.mbw;
             const int xb = mx * 48 + kk * 16, y = my * 16 + row;
             if (y < P.height)
                 h = load_piece(rows + (long long) (P.height - 1 - y) * P.stride + xb, P.width * 3 - xb, P.align);
@@ -449,8 +452,8 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
     // ---- B2: DCT + quantise.  8 lanes per PAIR of 8x8 blocks, 4 pairs (8 blocks) per warp per iteration: a lane
     //      carries row v (then column v) of two blocks in packed f32x2 registers, so every butterfly and quantiser
     //      operation is one FADD2 / FMUL2 / FFMA2 for both.  A pair's chunks are neighbours (types 0/1, 2/3, 4/5).
-    //      Iterations 0..15 take the luma pairs of two macroblocks each, 16..23 the chroma pairs of four; dealt
-    //      round-robin, every warp gets four (three luma + one chroma, or two + two).
+    //      Iterations 0..15 take the luma pairs of two macroblocks each, 16..23 the chroma pairs of four; every
+    //      warp gets four of one kind.
     {
         const int v = lane & 7, jb = lane >> 3;                   // v: my row in pass 1, my column in pass 2
         uint8_t* const trg = S.work + SAMP_BYTES + warp * TR_BYTES + jb * TR_GROUP + (jb >> 1) * 64 + (jb & 1) * 64;
@@ -462,16 +465,18 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
         uint32_t pos[8];                             // shared-space address of coefficient (u, v) of chunk 0
 #pragma unroll
         for (int u = 0; u < 8; u++) pos[u] = smem_addr(S.raw) + (uint32_t) unscan_rt(8 * u + v);
-        int table = -1;
         constexpr int LUMA_IT = TILE_MB / 2, ALL_IT = LUMA_IT + TILE_MB / 4;
-#pragma unroll 1
-        for (int it = warp; it < ALL_IT; it += NWARPS) {
-            const bool chroma = it >= LUMA_IT;
-            if ((int) chroma != table) {             // (warp-uniform)
-                table = (int) chroma;
+        // two warps in three take luma pairs only, the third chroma pairs only (there are twice as many luma pairs):
+        // every warp loads its quantiser constants once
+        constexpr int LUMA_WARPS = NWARPS * 2 / 3;
+        static_assert(NWARPS % 3 == 0 && LUMA_IT % LUMA_WARPS == 0 && (ALL_IT - LUMA_IT) % (NWARPS - LUMA_WARPS) == 0 &&
+                      LUMA_IT / LUMA_WARPS == (ALL_IT - LUMA_IT) / (NWARPS - LUMA_WARPS), "B2 iterations do not divide evenly");
+        const bool chroma = warp >= LUMA_WARPS;
 #pragma unroll
-                for (int u = 0; u < 8; u++) { gk[u] = d_gk[table][8 * u + v]; gc[u] = d_gc[table][8 * u + v]; }
-            }
+        for (int u = 0; u < 8; u++) { gk[u] = d_gk[chroma][8 * u + v]; gc[u] = d_gc[chroma][8 * u + v]; }
+        const int it_end = chroma ? ALL_IT : LUMA_IT, it_step = chroma ? NWARPS - LUMA_WARPS : LUMA_WARPS;
+#pragma unroll 1
+        for (int it = chroma ? LUMA_IT + warp - LUMA_WARPS : warp; it < it_end; it += it_step) {
             // macroblock and pair: luma pairs are (Y00, Y01) and (Y10, Y11), chunk types 0 and 2; the chroma pair is type 4
             const int mb = chroma ? 4 * (it - LUMA_IT) + jb : 2 * it + (jb >> 1);
             const int type = chroma ? 4 : (jb & 1) << 1;
@@ -624,11 +629,12 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
         }
         uint32_t lo = 0, hi = 0;
 #pragma unroll
-        for (int i = 0; i < 16; i++) {
-            // 0x80 in every non-zero byte, then gather the four flags into a nibble
-            uint32_t nz = (((w[i] & 0x7f7f7f7fu) + 0x7f7f7f7fu) | w[i]) & 0x80808080u;
-            uint32_t nib = ((nz >> 7) * 0x10204080u) >> 28;
-            if (i < 8) lo |= nib << (4 * i); else hi |= nib << (4 * (i - 8));
+        for (int i = 15; i >= 0; i--) {
+            // 0x80 in every non-zero byte; one multiply gathers the four flags (bits 7, 15, 23, 31) in bits 28..31 (the
+            // partial products below bit 24 cannot carry that far); a funnel shift pushes the nibble into the mask
+            const uint32_t nz = (((w[i] & 0x7f7f7f7fu) + 0x7f7f7f7fu) | w[i]) & 0x80808080u;
+            const uint32_t g = nz * 0x00204081u;
+            if (i < 8) lo = __funnelshift_l(g, lo, 4); else hi = __funnelshift_l(g, hi, 4);
         }
         const int8_t* cbase = reinterpret_cast<const int8_t*>(S.raw);
         auto coef = [&](int i) -> int { return (int) cbase[coef_byte(tid, i)]; };
@@ -666,7 +672,7 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
     // optional per-chunk outputs (tests, decode side-info) need the coefficient buffer: before it is reused
     if (P.qcoef != nullptr) {
         if (my_mb < n_mb) {
-            uint32_t* dst = reinterpret_cast<uint32_t*>(P.qcoef + ((long long) (tile / P.tiles_per_frame) * (P.mb1 - P.mb0) * 6 + (long long) (mb_first - P.mb0) * 6 + tid) * 64);
+            uint32_t* dst = reinterpret_cast<uint32_t*>(P.qcoef + ((long long) frame * (P.mb1 - P.mb0) * 6 + (long long) (mb_first - P.mb0) * 6 + tid) * 64);
 #pragma unroll
             for (int i = 0; i < 16; i++) dst[i] = reinterpret_cast<const uint32_t*>(S.raw)[coef_word(tid, i)];
         }
@@ -681,16 +687,25 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
         // completion order), leave (where, how many bytes) for enc_scan_tiles / enc_gather_tiles.
         if (tid == 0) {
             const unsigned units = (total + 15u) >> 4;
-            const unsigned at = atomicAdd(P.stage_cursor, units);
+            // a staging buffer that holds the worst case of every tile gives each tile its own slot: no round trip to
+            // the cursor in global memory (about a microsecond during which the CTA's other threads wait at the barrier below)
+            const unsigned at = P.stage_slot_units ? (unsigned) tile * P.stage_slot_units : atomicAdd(P.stage_cursor, units);
             S.tile_base = at;
             P.tile_info[tile] = make_uint2(at, total);
             if (P.bucket != nullptr) atomicAdd(P.bucket + (tile >> 6), total);      // the gather pass adds up 64 tiles at a time
             if ((unsigned long long) at + units > P.stage_cap_units) atomicOr(P.err, 1u);
         }
         if (compact_ok) {
-            const uint8_t* src = S.work + tid * SLOT;
+            const uint32_t* src = reinterpret_cast<const uint32_t*>(S.work + tid * SLOT);      // (slots are word aligned)
             uint8_t* dst = compact + my_off;
-            for (uint32_t i = 0; i < my_len; i++) dst[i] = src[i];
+#pragma unroll 1
+            for (uint32_t i = 0; i < my_len; i += 4) {
+                const uint32_t w = src[i >> 2];
+                dst[i] = (uint8_t) w;
+                if (i + 1 < my_len) dst[i + 1] = (uint8_t) (w >> 8);
+                if (i + 2 < my_len) dst[i + 2] = (uint8_t) (w >> 16);
+                if (i + 3 < my_len) dst[i + 3] = (uint8_t) (w >> 24);
+            }
         }
         PHASE_MARK(10);
         __syncthreads();
@@ -698,15 +713,17 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
         const unsigned long long at = S.tile_base;
         const bool fits = at + ((total + 15u) >> 4) <= P.stage_cap_units;
         if (P.chunk_off != nullptr && my_mb < n_mb)
-            P.chunk_off[(long long) (tile / P.tiles_per_frame) * (P.mb1 - P.mb0) * 6 + (long long) (mb_first - P.mb0) * 6 + tid] = my_off;          // tile-relative; the gather pass adds the tile's offset
+            P.chunk_off[(long long) frame * (P.mb1 - P.mb0) * 6 + (long long) (mb_first - P.mb0) * 6 + tid] = my_off;          // tile-relative; the gather pass adds the tile's offset
         if (fits) {
             uint8_t* out = P.stage + at * 16;
             if (compact_ok) {
                 const uint4* c4 = reinterpret_cast<const uint4*>(compact);
                 uint4* o4 = reinterpret_cast<uint4*>(out);
+#pragma unroll 1
                 for (uint32_t j = tid; j < ((total + 15u) >> 4); j += THREADS) o4[j] = c4[j];
             } else {                                     // oversized tile (> 64 B per chunk on average): chunk by chunk
                 const uint8_t* src = S.work + tid * SLOT;
+#pragma unroll 1
                 for (uint32_t i = 0; i < my_len; i++) out[my_off + i] = src[i];
             }
         }
@@ -760,6 +777,7 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
     if (compact_ok) {
         const uint8_t* src = S.work + tid * SLOT;
         uint8_t* dst = compact + my_off;
+#pragma unroll 1
         for (uint32_t i = 0; i < my_len; i++) dst[i] = src[i];
     }
     __syncthreads();
@@ -770,7 +788,7 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
         const bool fits = base + total <= P.out_cap;
         if (!fits && tid == 0) atomicOr(P.err, 1u);
         if (P.chunk_off != nullptr && my_mb < n_mb)
-            P.chunk_off[(long long) (tile / P.tiles_per_frame) * (P.mb1 - P.mb0) * 6 + (long long) (mb_first - P.mb0) * 6 + tid] = (uint32_t) (base + my_off);
+            P.chunk_off[(long long) frame * (P.mb1 - P.mb0) * 6 + (long long) (mb_first - P.mb0) * 6 + tid] = (uint32_t) (base + my_off);
         if (fits && compact_ok) {
             uint8_t* out = P.out + base;
             const uint32_t head = min(total, (uint32_t) ((4 - (reinterpret_cast<uintptr_t>(out) & 3)) & 3));
@@ -779,6 +797,7 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
             const uint32_t* cw = reinterpret_cast<const uint32_t*>(compact);
             uint32_t* ow = reinterpret_cast<uint32_t*>(out + head);
             const uint32_t sh = head * 8;
+#pragma unroll 1
             for (uint32_t j = tid; j < n_words; j += THREADS) {
                 // bytes compact[head + 4j .. +4): two aligned words, funnel-shifted
                 uint32_t lo = cw[j], hi = cw[j + 1];
@@ -789,6 +808,7 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
         } else if (fits) {                              // oversized tile: chunk by chunk
             const uint8_t* src = S.work + tid * SLOT;
             uint8_t* dst = P.out + base + my_off;
+#pragma unroll 1
             for (uint32_t i = 0; i < my_len; i++) dst[i] = src[i];
         }
     }
@@ -1009,6 +1029,8 @@ cudaError_t launch_encode(const EncParams& P, int n_tiles, cudaStream_t stream) 
     Q.n_tiles = n_tiles;
     if (Q.compact_cap <= 0 || Q.compact_cap > COMPACT_CAP) Q.compact_cap = COMPACT_CAP;
     if (Q.tiles_per_frame <= 0) { Q.tiles_per_frame = n_tiles; Q.frame_stride = 0; }      // a single frame
+    Q.div_mbw = make_fastdiv((uint32_t) Q.mbw);
+    Q.div_tpf = make_fastdiv((uint32_t) Q.tiles_per_frame);
     if (n_tiles <= ENC_FUSED_MAX_TILES || n_tiles > 64 * ENC_BUCKETS) Q.bucket = nullptr;   // (the kernel adds into them only where the gather pass reads them)
     cudaError_t le = launch_pdl(awi_encode_kernel, (unsigned) n_tiles, THREADS, sizeof(EncSmem), stream, Q);
     if (le != cudaSuccess) return le;

@@ -5,6 +5,7 @@
 #include <stdint.h>
 #include <stddef.h>
 #include "codec_tables.h"
+#include "codec_math.cuh"
 
 namespace awi {
 
@@ -65,6 +66,7 @@ struct EncParams {
     int mbw;                      // macroblocks per row
     int mb0, mb1;                 // raster macroblock range [mb0, mb1) to encode (of every frame of a batch)
     int tiles_per_frame;          // batches: tiles per frame (0 = single frame); the grid covers frames x tiles
+    FastDiv div_mbw, div_tpf;     // filled by launch_encode: division by mbw and by tiles_per_frame
     long long frame_stride;       // batches: bytes between consecutive frames' pixel arrays
     unsigned long long* frame_off;  // batches, optional: n_frames+1 payload offsets (two-pass mode)
     int sm_count;                 // filled by launch_encode
@@ -81,6 +83,7 @@ struct EncParams {
     // enc_scan_tiles + enc_gather_tiles move them to their payload offsets
     uint8_t* stage;               // 16-byte aligned
     unsigned long long stage_cap_units;   // capacity in 16-byte units
+    unsigned int stage_slot_units;        // non-zero: tile t is staged at unit t * stage_slot_units (the buffer holds every tile's worst case)
     unsigned int* stage_cursor;   // zero before the first launch; enc_scan_tiles leaves it at zero again
     unsigned int* bucket;         // optional, ENC_BUCKETS words, zero before the first launch: byte counts per 64 tiles (left at zero again)
     unsigned int* gather_done;    // with `bucket`: one word, zero before the first launch

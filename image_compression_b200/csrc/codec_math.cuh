@@ -75,6 +75,26 @@ AWI_HD uint32_t umulhi32(uint32_t a, uint32_t b) {
     return (uint32_t) (((uint64_t) a * b) >> 32);
 #endif
 }
+// Division of 0 <= n < 2^31 by a launch-invariant d >= 1 as one 32x32->hi multiply and a shift (the compiler's general
+// 32-bit division is about twenty instructions, and every thread of the encode kernel needs two per tile).
+// l = ceil(log2 d), mul = floor(2^(31+l) / d) + 1 < 2^32: mul * d - 2^(31+l) lies in (0, d], so the error of
+// n * mul / 2^(31+l) against n / d stays below 1/d and the floor is exact.  d == 1 is marked by mul == 0.
+struct FastDiv {
+    uint32_t mul, shift;
+};
+inline FastDiv make_fastdiv(uint32_t d) {
+    FastDiv f = {0u, 0u};
+    if (d <= 1u) return f;
+    uint32_t l = 0;
+    while ((1ull << l) < d) l++;
+    f.mul = (uint32_t) ((1ull << (31 + l)) / d + 1ull);
+    f.shift = l - 1u;
+    return f;
+}
+AWI_HD int fast_div(int n, FastDiv f) {
+    return f.mul ? (int) (umulhi32((uint32_t) n, f.mul) >> f.shift) : n;
+}
+
 AWI_HD uint32_t byte_perm(uint32_t a, uint32_t b, uint32_t s) {
 #if defined(__CUDA_ARCH__)
     return __byte_perm(a, b, s);
@@ -418,7 +438,8 @@ AWI_HD int rle_chunk(int dc, int prev_dc, uint64_t nzmask, Coef coef, Put put32)
         m &= m - 1;
         int gap = i - prev - 1;
         prev = i;
-        for (int z = gap >> 4; z > 0; z--) bits_push(s, 0xF0u, 8, put32);               // rle.c:70-83
+#pragma unroll 1
+        for (int z = gap >> 4; z > 0; z--) bits_push(s, 0xF0u, 8, put32);               // rle.c:70-83 (rare: kept small)
         int v = coef(i);
         int size = bit_length_u((uint32_t) (v < 0 ? -v : v));
         uint32_t field = (uint32_t) (v + (v >> 31)) & ((1u << size) - 1u);              // rle.c:86-92: v, or v - 1 in `size` bits

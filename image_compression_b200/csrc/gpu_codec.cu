@@ -422,7 +422,12 @@ bool encode_dev_impl(Ctx* c, const uint8_t* d_rows, int width, int height, long 
     // two-pass encode: tiles go to a staging buffer in completion order (no tile ever waits for
     // another), then a scan + gather place them; scratch = header + (where,bytes) + offset per tile
     const size_t ws_bytes = ENC_WS_HEADER + (size_t) n_tiles * 16;
-    const size_t stage_bytes = cap + (size_t) n_tiles * 16 + 256;
+    // a payload capacity that covers the worst case (every chunk 121 bytes) lets every tile have its own staging slot;
+    // a tighter capacity (the caller knows its content) keeps the staging buffer as small as the payload
+    constexpr size_t SLOT_UNITS = ((size_t) awi::ENC_TILE_MB * 6 * 121 + 15) / 16;
+    static const bool slots_allowed = getenv("GPU_CODEC_NO_STAGE_SLOTS") == nullptr;      // (measurement knob)
+    const bool slots = slots_allowed && cap >= (size_t) n_mb * n_frames * 6 * 121 && (size_t) n_tiles * SLOT_UNITS < (1ull << 32);
+    const size_t stage_bytes = slots ? (size_t) n_tiles * SLOT_UNITS * 16 + 256 : cap + (size_t) n_tiles * 16 + 256;
     const size_t ws_before = c->enc_ws.bytes;
     if (!ensure(c->enc_ws, ws_bytes) || !ensure(c->enc_stage, stage_bytes)) return false;
     // the staging cursor must be zero when a launch starts: once here for a fresh buffer, afterwards the scan
@@ -448,6 +453,7 @@ bool encode_dev_impl(Ctx* c, const uint8_t* d_rows, int width, int height, long 
     P.desc = nullptr;
     P.stage = c->enc_stage.p;
     P.stage_cap_units = (stage_bytes - 256) / 16;
+    P.stage_slot_units = slots ? (unsigned int) SLOT_UNITS : 0u;
     P.stage_cursor = reinterpret_cast<unsigned int*>(c->enc_ws.p + 16);
     P.gather_done = reinterpret_cast<unsigned int*>(c->enc_ws.p + 24);
     P.bucket = reinterpret_cast<unsigned int*>(c->enc_ws.p + 256);

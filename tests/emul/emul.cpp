@@ -37,6 +37,27 @@ static int transform(const uint8_t* px, int* chunk) {
 
 extern "C" {
 
+// Checks fast_div(n, make_fastdiv(d)) == n / d for every n in the list and every d in [d0, d1); returns the first
+// failing d (and its n through *bad_n), or 0.
+uint32_t emul_fastdiv_check(uint32_t d0, uint32_t d1, const int32_t* ns, int n_ns, int32_t* bad_n) {
+    for (uint32_t d = d0; d < d1; d++) {
+        const FastDiv f = make_fastdiv(d);
+        for (int i = 0; i < n_ns; i++) {
+            int32_t n = ns[i];
+            if (fast_div(n, f) != (int) ((uint32_t) n / d)) { *bad_n = n; return d; }
+        }
+        // the neighbourhood of multiples of d near the top of the range, where an inexact multiplier fails first
+        for (uint32_t q = 0x7fffffffu / d, k = 0; k < 3 && q > 0; k++, q--)
+            for (int e = -1; e <= 0; e++) {
+                const uint64_t n64 = (uint64_t) q * d + (uint64_t) (int64_t) e;
+                if (n64 > 0x7fffffffull) continue;
+                const int32_t n = (int32_t) n64;
+                if (fast_div(n, f) != (int) ((uint32_t) n / d)) { *bad_n = n; return d; }
+            }
+    }
+    return 0;
+}
+
 int emul_transform(const uint8_t* px, int chroma, int* chunk) {
     return chroma ? transform<true>(px, chunk) : transform<false>(px, chunk);
 }

@@ -216,3 +216,17 @@ def test_kernel_flag_expression_is_safe(emul, port):
             want = port.transform(b, chroma)
             for i in np.nonzero(chunk != want)[0]:
                 assert (amb.value >> int(scan[i])) & 1, "unflagged fast-path mismatch under the kernel's flag expression"
+
+
+def test_invariant_divisor_division(emul):
+    """fast_div (one multiply-high and a shift in the encode kernel's prologue) equals integer division for every
+    divisor a frame can produce (macroblocks per row <= 4096, tiles per frame < 2^20) and numerators below 2^31."""
+    rng = np.random.default_rng(5)
+    ns = np.concatenate([np.arange(0, 70), rng.integers(0, 2 ** 31, 400), [2 ** 31 - 1, 2 ** 31 - 2, 2 ** 30, 2 ** 30 - 1]])
+    ns = np.ascontiguousarray(ns, np.int32)
+    bad = C.c_int32()
+    emul.emul_fastdiv_check.restype = C.c_uint32
+    nsp = ns.ctypes.data_as(i32p)
+    for d0, d1 in ((1, 70000), (2 ** 20 - 500, 2 ** 20 + 500), (2 ** 30 - 50, 2 ** 30 + 1)):
+        d = emul.emul_fastdiv_check(C.c_uint32(d0), C.c_uint32(d1), nsp, len(ns), C.byref(bad))
+        assert d == 0, (d, bad.value)
