@@ -427,13 +427,12 @@ AWI_HD int rle_chunk(int dc, int prev_dc, uint64_t nzmask, Coef coef, Put put32)
     BitAcc s;
     int diff = dc - prev_dc;
     bits_push(s, (uint32_t) (diff >= 0 ? diff : 4095 + diff) & 0xFFFu, 12, put32);      // rle.c:53-57
-    int prev = 0, base = 0;
-    uint32_t m = (uint32_t) nzmask & ~1u, next = (uint32_t) (nzmask >> 32);             // positions 1..31, then 32..63
-    while (true) {
-        if (m == 0) {
-            if (next == 0) break;
-            m = next; next = 0; base = 32;
-        }
+    int prev = 0;
+    // positions 1..31, then 32..63: one loop body, run once per half of the mask (no "which half" test per symbol)
+#pragma unroll 1
+    for (int base = 0; base < 64; base += 32) {
+    uint32_t m = base ? (uint32_t) (nzmask >> 32) : (uint32_t) nzmask & ~1u;
+    while (m != 0) {
         int i = base + lowest_set32(m);
         m &= m - 1;
         int gap = i - prev - 1;
@@ -444,6 +443,7 @@ AWI_HD int rle_chunk(int dc, int prev_dc, uint64_t nzmask, Coef coef, Put put32)
         int size = bit_length_u((uint32_t) (v < 0 ? -v : v));
         uint32_t field = (uint32_t) (v + (v >> 31)) & ((1u << size) - 1u);              // rle.c:86-92: v, or v - 1 in `size` bits
         bits_push(s, ((uint32_t) ((gap & 15) << 4 | size) << size) | field, 8 + size, put32);
+    }
     }
     bits_push(s, 0u, 8, put32);                                                          // EOB, rle.c:106
     int nbytes = 4 * s.words + ((s.cnt + 7) >> 3);                                        // rle.c:107 pad
