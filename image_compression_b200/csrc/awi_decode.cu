@@ -472,25 +472,30 @@ __device__ __forceinline__ void store_px(const DecParams& P, int x, int y, int r
 }
 
 __global__ void __launch_bounds__(REC_THREADS) dec_reconstruct(DecParams P, const uint32_t* __restrict__ chunk_off,
-                                                               const int* __restrict__ dcabs, unsigned int* err) {
+                                                               const int* __restrict__ dcabs, unsigned int* err,
+                                                               FastDiv div_tiles_per_row) {
     pdl_wait();
     pdl_trigger();
     extern __shared__ __align__(16) unsigned char smem_raw[];
     RecSmem& S = *reinterpret_cast<RecSmem*>(smem_raw);
     const int tid = threadIdx.x;
     const int tiles_per_row = (P.mbw + REC_MB - 1) / REC_MB;
-    const int my = P.mb_row0 + blockIdx.x / tiles_per_row;
-    const int mx0 = (blockIdx.x % tiles_per_row) * REC_MB;
+    const int row_in = fast_div((int) blockIdx.x, div_tiles_per_row);
+    const int my = P.mb_row0 + row_in;
+    const int mx0 = ((int) blockIdx.x - row_in * tiles_per_row) * REC_MB;
     const int n_mb = min(REC_MB, P.mbw - mx0);
     const long long chunk0 = ((long long) my * P.mbw + mx0) * 6;
     const int n_ch = n_mb * 6;
-    if (*reinterpret_cast<volatile unsigned int*>(err) != 0) return;          // an earlier stage rejected the stream
+    // (the flag and the offsets below are all requested before the first of them is looked at; the offsets array
+    // exists whatever the flag says)
+    const unsigned int rejected = *reinterpret_cast<volatile unsigned int*>(err);
 
     // the tile's chunks are contiguous in the stream: [b0, b1)
     const uint32_t b0 = chunk_off[chunk0], b1_raw = chunk_off[chunk0 + n_ch];
     uint32_t my_off = 0;
     int my_dc = 0;
     if (tid < n_ch) { my_off = chunk_off[chunk0 + tid]; my_dc = dcabs[chunk0 + tid]; }      // in flight during staging
+    if (rejected != 0) return;                                                // an earlier stage rejected the stream
     uint32_t b1 = b1_raw;
     // With the encoder's side-info the end of the last chunk is not known, only the end of the payload: whatever
     // follows the last chunk is ignored (as the reference does, awi.c:184-217), so the last tile's slice is cut
@@ -575,15 +580,25 @@ __global__ void __launch_bounds__(REC_THREADS) dec_reconstruct(DecParams P, cons
         const int blk = tid / REC_TPB, y0 = (tid % REC_TPB) * REC_ROWS;
         if (blk < n_ch) {
             double sum[REC_ROWS][8];
+            unsigned long long m = S.mask[blk];
+            const int* cf = S.coef[blk];
+            // The DC term is the same for all 64 samples: cos_table[.][0] is 1.0f, so ((cu*cv*coef) * 1.0) * 1.0 is the
+            // first product itself and 0.0 + it is exact: the sums start from it instead of taking a turn of the loop.
+            double first = 0.0;
+            if (m & 1ull) { first = __dmul_rn(S.cucv[0], (double) cf[0]); m &= ~1ull; }
 #pragma unroll
             for (int r = 0; r < REC_ROWS; r++)
 #pragma unroll
-                for (int x = 0; x < 8; x++) sum[r][x] = 0.0;
-            unsigned long long m = S.mask[blk];
-            const int* cf = S.coef[blk];
-            while (m) {
-                const int k = __ffsll((long long) m) - 1;
-                m &= m - 1;
+                for (int x = 0; x < 8; x++) sum[r][x] = first;
+            // the mask as two words, the lower non-empty one served first: a dozen instructions of loop control per
+            // coefficient instead of the two dozen that 64-bit find-first-set / clear-lowest / test compile to
+            uint32_t lo = (uint32_t) m, hi = (uint32_t) (m >> 32);
+            while ((lo | hi) != 0u) {
+                const bool low = lo != 0u;
+                const uint32_t t = low ? lo : hi, rest = t & (t - 1u);
+                const int k = (__ffs((int) t) - 1) + (low ? 0 : 32);
+                lo = low ? rest : 0u;
+                hi = low ? hi : rest;
                 const int u = k >> 3, v = k & 7;
                 const double a = __dmul_rn(S.cucv[k], (double) cf[k]);
                 double b[REC_ROWS];
@@ -778,7 +793,8 @@ cudaError_t launch_decode(const DecParams& P, void* workspace, size_t workspace_
     const int tiles_per_row = (P.mbw + REC_MB - 1) / REC_MB;
     const int rows = P.mb_row1 - P.mb_row0;
     if (rows > 0)
-        launch_pdl(dec_reconstruct, (unsigned) (tiles_per_row * rows), REC_THREADS, sizeof(RecSmem), stream, P, chunk_off, dcabs, err);
+        launch_pdl(dec_reconstruct, (unsigned) (tiles_per_row * rows), REC_THREADS, sizeof(RecSmem), stream, P, chunk_off, dcabs, err,
+                   make_fastdiv((uint32_t) tiles_per_row));
     return cudaGetLastError();
 }
 

@@ -230,3 +230,11 @@ def test_invariant_divisor_division(emul):
     for d0, d1 in ((1, 70000), (2 ** 20 - 500, 2 ** 20 + 500), (2 ** 30 - 50, 2 ** 30 + 1)):
         d = emul.emul_fastdiv_check(C.c_uint32(d0), C.c_uint32(d1), nsp, len(ns), C.byref(bad))
         assert d == 0, (d, bad.value)
+
+
+def test_cosine_table_first_column_is_one(emul):
+    """dec_reconstruct starts its sums from the DC product instead of adding it in a loop turn: valid because
+    cos_table[.][0] (dct.c:14-23) is exactly 1.0f, so ((cu*cv*coef) * 1.0) * 1.0 is the product itself."""
+    bits = np.zeros(64, np.uint32)
+    emul.emul_cos_bits(bits.ctypes.data_as(C.POINTER(C.c_uint32)))
+    assert (bits.reshape(8, 8)[:, 0] == 0x3F800000).all()
