@@ -601,10 +601,15 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
             int u = k >> 3, v = k & 7;
             int y = lane >> 2, x0 = (lane & 3) * 2;
             float cyu = __uint_as_float(cos_bits_rt(y * 8 + u));
-            double part = (double) exact_product(sample_of(samp, b, y, x0) - 128, cyu, __uint_as_float(cos_bits_rt(x0 * 8 + v)));
-            part += (double) exact_product(sample_of(samp, b, y, x0 + 1) - 128, cyu, __uint_as_float(cos_bits_rt((x0 + 1) * 8 + v)));
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+            // The 64 products are multiples of 2^-28 below 2^7 (codec_math.cuh, exact path), so their sum is an integer
+            // number of 2^-28 below 2^41: added up as integers, 20 low bits and the rest apart, by two warp reductions
+            // (REDUX) instead of five rounds of 64-bit shuffles and fp64 additions - the whole CTA is waiting for this.
+            const float p0 = exact_product(sample_of(samp, b, y, x0) - 128, cyu, __uint_as_float(cos_bits_rt(x0 * 8 + v)));
+            const float p1 = exact_product(sample_of(samp, b, y, x0 + 1) - 128, cyu, __uint_as_float(cos_bits_rt((x0 + 1) * 8 + v)));
+            const long long mine = __float2ll_rz(p0 * 268435456.0f) + __float2ll_rz(p1 * 268435456.0f);      // exact: powers of two
+            const int lo_sum = __reduce_add_sync(0xffffffffu, (int) (mine & 0xfffff));
+            const int hi_sum = __reduce_add_sync(0xffffffffu, (int) (mine >> 20));
+            const double part = (double) (((long long) hi_sum << 20) + lo_sum) * 3.7252902984619140625e-9;     // * 2^-28, exact
             if (lane == 0) {
                 int c = exact_coef_finish(part, u, v);
                 int q = quant_int(c, chroma ? qchroma_rt(k) : qluma_rt(k));
