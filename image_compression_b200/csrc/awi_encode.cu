@@ -544,10 +544,13 @@ __global__ void __launch_bounds__(THREADS, ENC_MIN_CTAS) awi_encode_kernel(EncPa
 #pragma unroll
                     for (int u = 0; u < 8; u++) {
                         if (u > 0 || v > 0) {
+                            // here, off the fast path, every position gets its own threshold (the fast path tests the
+                            // running maximum against the tightest one): two to five times fewer coefficients go to phase C
                             float x0, x1, tmp;
                             f2_unpack(d[u], x0, x1);
-                            if (quant_absdiff(x0, gk[u], gc[u], tmp) > AWI_GT_MIN_LUMA) m0 |= 1ull << (8 * u + v);
-                            if (quant_absdiff(x1, gk[u], gc[u], tmp) > AWI_GT_MIN_LUMA) m1 |= 1ull << (8 * u + v);
+                            const float gt = d_gt[chroma][8 * u + v];
+                            if (quant_absdiff(x0, gk[u], gc[u], tmp) > gt) m0 |= 1ull << (8 * u + v);
+                            if (quant_absdiff(x1, gk[u], gc[u], tmp) > gt) m1 |= 1ull << (8 * u + v);
                         }
                     }
                     // the lane that turns a chunk's mask from zero to non-zero lists the chunk (once)

@@ -100,9 +100,10 @@ void emul_fast_vs_exact(const uint8_t* px, double* fast_scaled, double* exact_t)
     }
 }
 
-// The encode kernel's own flag expression (awi_encode.cu phase B2): ONE threshold for every position, the tightest of
-// the table (AWI_GT_MIN_*), compared with |g - rn(g)| of each coefficient; the DC position is never flagged.
-// Returns the fast-path chunk and the flag mask (natural positions).
+// The encode kernel's own flag expression (awi_encode.cu phase B2), two levels: a lane (one column v of the block) keeps
+// the running maximum of |g - rn(g)| over its eight positions and compares it with ONE threshold, the tightest of the
+// table (AWI_GT_MIN_*); only a lane that exceeds it looks at its positions one by one, each against its own threshold
+// from the table.  The DC position is never flagged.  Returns the fast-path chunk and the flag mask (natural positions).
 void emul_fast_kernel_flags(const uint8_t* px, int chroma, int* chunk, uint64_t* amb_out) {
     float d[64];
     for (int i = 0; i < 64; i++) d[i] = centred(px[i]);
@@ -110,14 +111,24 @@ void emul_fast_kernel_flags(const uint8_t* px, int chroma, int* chunk, uint64_t*
         aan8(d[8 * y + 0], d[8 * y + 1], d[8 * y + 2], d[8 * y + 3], d[8 * y + 4], d[8 * y + 5], d[8 * y + 6], d[8 * y + 7]);
     for (int x = 0; x < 8; x++)
         aan8(d[x], d[8 + x], d[16 + x], d[24 + x], d[32 + x], d[40 + x], d[48 + x], d[56 + x]);
-    const float gt = chroma ? AWI_GT_MIN_CHROMA : AWI_GT_MIN_LUMA;
+    const float gt_min = chroma ? AWI_GT_MIN_CHROMA : AWI_GT_MIN_LUMA;
     uint64_t amb = 0;
     int q[64];
+    float dist[64];
+    dist[0] = 0.0f;
     for (int k = 1; k < 64; k++) {
         float t;
-        const float dist = quant_absdiff(d[k], chroma ? gk_chroma(k) : gk_luma(k), chroma ? gc_chroma(k) : gc_luma(k), t);
-        if (dist > gt) amb |= 1ull << k;
+        dist[k] = quant_absdiff(d[k], chroma ? gk_chroma(k) : gk_luma(k), chroma ? gc_chroma(k) : gc_luma(k), t);
         q[k] = (int) (int8_t) (f2u(t) & 0xffu);
+    }
+    for (int v = 0; v < 8; v++) {
+        float worst = 0.0f;
+        for (int u = 0; u < 8; u++) worst = dist[8 * u + v] > worst ? dist[8 * u + v] : worst;
+        if (worst > gt_min)
+            for (int u = 0; u < 8; u++) {
+                const int k = 8 * u + v;
+                if (k > 0 && dist[k] > (chroma ? gt_chroma(k) : gt_luma(k))) amb |= 1ull << k;
+            }
     }
     q[0] = quant_int(dc_coef_from_sum((int) d[0]), chroma ? 17 : 16);
     for (int i = 0; i < 64; i++) chunk[i] = q[scan_tab(i)];
