@@ -210,7 +210,9 @@ AWI_HD ChromaTerms chroma_terms(int cb, int cr) {
     const uint32_t m = (uint32_t) (17000000 - 43017 * kb - 89267 * kr);      // eighths of 1e-6; |43017 kb + 89267 kr| < 16.94e6
     const uint32_t q = umulhi32(m, 140737489u) >> 12;
     t.g_add = (int) q - 136;
-    t.g_on_integer = m - q * 125000u == 0u;
+    // (three pairs in 65536: (28,228), (228,28) and the neutral (128,128); the neutral one needs no special case, its
+    // green term is 0 and y - 0.0 - 0.0 is y in fp64 as well, which is what y + g_add gives)
+    t.g_on_integer = m - q * 125000u == 0u && (kb | kr) != 0;
     return t;
 }
 AWI_HD int clamp255(int v) { return v < 0 ? 0 : (v > 255 ? 255 : v); }

@@ -492,3 +492,45 @@ def test_side_info_decode_ignores_long_tail(gpu, port):
             gpu.decode_dev(0, qt, qt.numel(), w, h, dst, stride, chunk_off=side)
             gpu.sync_check(0)
             assert dst.cpu().numpy().tobytes() == want, (tail, side is None)
+
+
+@pytest.mark.gpu
+def test_green_on_integer_pairs_through_the_decoder(gpu, port):
+    """The two (Cb, Cr) pairs whose green term is a non-zero integer, (28, 228) and (228, 28) (43017 kb + 89267 kr a
+    multiple of 125000), take the literal fp64 expression of color.c:62, out of line in dec_reconstruct.  Natural content
+    never produces them, so the payload is hand-made: one chroma block flat at 28 (a DC-only chunk), the other with a DC
+    and one AC coefficient chosen so that some of its samples are 228, luma blocks flat at several levels."""
+    flat28 = np.zeros(64, np.int32)
+    flat28[0] = -47
+    assert (port.inverse_transform(flat28, 1) == 28).all()
+    found = None
+    for dc in range(30, 65):
+        for ac in range(-40, 41):
+            c = np.zeros(64, np.int32)
+            c[0], c[1] = dc, ac
+            if (port.inverse_transform(c, 1) == 228).any():
+                found = c
+                break
+        if found is not None:
+            break
+    assert found is not None
+    n228 = int((port.inverse_transform(found, 1) == 228).sum())
+    w, h = 64, 16                                  # four macroblocks: both orientations, two luma settings each
+    chunks, prev = [], [0] * 6
+    for mb in range(4):
+        luma = [np.zeros(64, np.int32) for _ in range(4)]
+        for j in range(4):
+            luma[j][0] = (-60, -20, 15, 62)[(j + mb) % 4]
+            luma[j][2] = 3 * (mb - 1)              # a little texture, so that many y values meet the pair
+        cb, cr = (flat28, found) if mb % 2 == 0 else (found, flat28)
+        for t, c in enumerate(luma + [cb, cr]):
+            chunks.append(port.rle(c, prev[t]))
+            prev[t] = int(c[0])
+    p = np.frombuffer(b"".join(chunks), np.uint8).copy()
+    want, used = port.decode(p, w, h)
+    assert used == p.size and n228 > 0
+    got = gpu.decode_to_bgr(p, w, h)
+    assert np.asarray(got).tobytes() == want.tobytes()
+    rgb = gpu.decode_to_rgb24(p, w, h)
+    want_rgb, _ = port.decode(p, w, h, rgb_topdown=True)
+    assert np.asarray(rgb).tobytes() == want_rgb.tobytes()
